@@ -1,0 +1,577 @@
+// bvh_build.cu — scene flattening + GPU LBVH build (kernels K1-K3).
+//
+// Stands in for OptixRenderer::BuildAccel (Renderer/OptiX/OptixRenderer.cpp:
+// 306-456: per-mesh uploads :328-340, triangle build inputs with a FLOAT12
+// pre-transform :342-373, optixAccelBuild :416, optixAccelCompact :440),
+// CreateTextures (:562-612) and the material half of BuildSBT (:486-560).
+//
+//   k_flatten      one thread per triangle: world-space vertices/normals
+//                  (glm's mat4*vec4 association, devicePrograms.cu:77-81),
+//                  centroid bounds by block reduce + ordered-int atomics
+//   k_morton       63-bit Morton key of the box centre
+//   radix sort     stable LSD, 8 x 8-bit passes: k_rs_hist / k_rs_scan /
+//                  k_rs_scatter (warp match_any ranking; hand-written, no CUB)
+//   k_karras       Karras 2012 topology, one thread per internal node
+//   k_refit        bottom-up AABB refit with arrival counters
+//   k_emit_*       leaf-order triangle / normal / uv records and 64-byte nodes
+#include <vector>
+
+#include "scene.cuh"
+
+namespace b2pt {
+
+namespace {
+
+constexpr int kThreads = 256;
+inline int blocks_for(int64_t n, int threads = kThreads) { return (int)((n + threads - 1) / threads); }
+
+// ---- ordered-int encoding so float min/max can use integer atomics --------
+__device__ __forceinline__ uint32_t f2ord(float f) {
+    uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float ord2f(uint32_t u) {
+    u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(u);
+#else
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+#endif
+}
+
+struct BoundsOrd {
+    uint32_t lo[3], hi[3];      // centroid bounds
+    uint32_t vlo[3], vhi[3];    // vertex bounds
+};
+
+__global__ void k_init_bounds(BoundsOrd* b) {
+    for (int i = 0; i < 3; i++) {
+        b->lo[i] = b->vlo[i] = 0xffffffffu;
+        b->hi[i] = b->vhi[i] = 0u;
+    }
+}
+
+// K1a: world-space triangle soup + bounds.
+__global__ void __launch_bounds__(kThreads)
+k_flatten(int n_tris, const int32_t* __restrict__ indices, const uint32_t* __restrict__ tri_mesh,
+          const MeshInfo* __restrict__ meshes, const float* __restrict__ positions,
+          const float* __restrict__ normals, float3* __restrict__ wv, float3* __restrict__ wn,
+          BoundsOrd* bounds) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    float3 clo = v3(INFINITY), chi = v3(-INFINITY), vlo = v3(INFINITY), vhi = v3(-INFINITY);
+    if (g < n_tris) {
+        const MeshInfo& mi = meshes[tri_mesh[g]];
+        float3 p[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            const int vi = indices[3 * g + k] + mi.vtx_offset;
+            const float4 w = mat4_mul(mi.model, positions[3 * vi], positions[3 * vi + 1], positions[3 * vi + 2], 1.0f);
+            p[k] = v3(w.x, w.y, w.z);
+            wv[3 * g + k] = p[k];
+            float3 nw = v3(0.0f);
+            if (mi.has_normals) {
+                const float4 t = mat4_mul(mi.model, normals[3 * vi], normals[3 * vi + 1], normals[3 * vi + 2], 0.0f);
+                nw = v3(t.x, t.y, t.z);
+            }
+            wn[3 * g + k] = nw;
+        }
+        const Aabb bb = aabb_of_tri(p[0], p[1], p[2]);
+        vlo = bb.lo;
+        vhi = bb.hi;
+        clo = chi = (bb.lo + bb.hi) * 0.5f;
+    }
+    // warp reduce, then one atomic per warp and component
+    float r[12] = {clo.x, clo.y, clo.z, vlo.x, vlo.y, vlo.z, chi.x, chi.y, chi.z, vhi.x, vhi.y, vhi.z};
+#pragma unroll
+    for (int i = 0; i < 12; i++) {
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+            const float o = __shfl_xor_sync(0xffffffffu, r[i], off);
+            r[i] = i < 6 ? fminf(r[i], o) : fmaxf(r[i], o);
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+        for (int i = 0; i < 3; i++) {
+            if (r[i] <= r[6 + i]) {  // at least one valid triangle in the warp
+                atomicMin(&bounds->lo[i], f2ord(r[i]));
+                atomicMax(&bounds->hi[i], f2ord(r[6 + i]));
+                atomicMin(&bounds->vlo[i], f2ord(r[3 + i]));
+                atomicMax(&bounds->vhi[i], f2ord(r[9 + i]));
+            }
+        }
+    }
+}
+
+// K1b: Morton keys.
+__global__ void __launch_bounds__(kThreads)
+k_morton(int n_tris, const float3* __restrict__ wv, const BoundsOrd* __restrict__ bounds,
+         uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_tris) return;
+    const float3 lo = v3(ord2f(bounds->lo[0]), ord2f(bounds->lo[1]), ord2f(bounds->lo[2]));
+    const float3 hi = v3(ord2f(bounds->hi[0]), ord2f(bounds->hi[1]), ord2f(bounds->hi[2]));
+    const float3 ext = hi - lo;
+    const float3 inv = v3(ext.x > 0.0f ? 1.0f / ext.x : 0.0f, ext.y > 0.0f ? 1.0f / ext.y : 0.0f,
+                          ext.z > 0.0f ? 1.0f / ext.z : 0.0f);
+    const Aabb bb = aabb_of_tri(wv[3 * g], wv[3 * g + 1], wv[3 * g + 2]);
+    keys[g] = morton63((bb.lo + bb.hi) * 0.5f, lo, inv);
+    vals[g] = (uint32_t)g;
+}
+
+// ---- K2: stable LSD radix sort, 8 bits per pass ---------------------------
+constexpr int kRsWarps = 8;
+constexpr int kRsItems = 8;                                // 32-key steps per warp
+constexpr int kRsTile = kRsWarps * 32 * kRsItems;          // 2048 keys per block
+constexpr uint32_t kRsNoDigit = 0xffffu;
+
+__global__ void __launch_bounds__(kRsWarps * 32)
+k_rs_hist(int n, const uint64_t* __restrict__ keys, int shift, int n_tiles, uint32_t* __restrict__ hist) {
+    __shared__ uint32_t cnt[256];
+    cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const int base = blockIdx.x * kRsTile;
+    for (int i = threadIdx.x; i < kRsTile; i += blockDim.x) {
+        const int k = base + i;
+        if (k < n) atomicAdd(&cnt[(uint32_t)(keys[k] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    hist[threadIdx.x * n_tiles + blockIdx.x] = cnt[threadIdx.x];  // digit-major
+}
+
+// exclusive scan of `m` counters by ONE block (m = 256 * n_tiles, small)
+__global__ void __launch_bounds__(1024)
+k_rs_scan(int m, uint32_t* __restrict__ data) {
+    __shared__ uint32_t part[1024];
+    const int per = (m + 1023) / 1024;
+    const int lo = threadIdx.x * per, hi = min(lo + per, m);
+    uint32_t s = 0;
+    for (int i = lo; i < hi; i++) s += data[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    for (int off = 1; off < 1024; off <<= 1) {  // Hillis-Steele inclusive scan
+        uint32_t v = threadIdx.x >= off ? part[threadIdx.x - off] : 0;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    uint32_t run = threadIdx.x ? part[threadIdx.x - 1] : 0;
+    for (int i = lo; i < hi; i++) {
+        const uint32_t v = data[i];
+        data[i] = run;
+        run += v;
+    }
+}
+
+__global__ void __launch_bounds__(kRsWarps * 32)
+k_rs_scatter(int n, const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+             uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int shift, int n_tiles,
+             const uint32_t* __restrict__ hist) {
+    __shared__ uint32_t cnt[kRsWarps][256];   // per-warp digit counts -> running offsets
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < kRsWarps * 256; i += blockDim.x) (&cnt[0][0])[i] = 0;
+    __syncthreads();
+    const int wbase = blockIdx.x * kRsTile + warp * (32 * kRsItems);
+    uint64_t key[kRsItems];
+    uint32_t dig[kRsItems];
+#pragma unroll
+    for (int s = 0; s < kRsItems; s++) {
+        const int k = wbase + s * 32 + lane;
+        key[s] = k < n ? keys_in[k] : 0;
+        dig[s] = k < n ? ((uint32_t)(key[s] >> shift) & 255u) : kRsNoDigit;
+        const uint32_t peers = __match_any_sync(0xffffffffu, dig[s]);
+        if (dig[s] != kRsNoDigit && lane == __ffs(peers) - 1) cnt[warp][dig[s]] += __popc(peers);
+        __syncwarp();
+    }
+    __syncthreads();
+    {   // thread d: turn per-warp counts of digit d into exclusive offsets + global base
+        const int d = threadIdx.x;
+        uint32_t run = hist[d * n_tiles + blockIdx.x];
+#pragma unroll
+        for (int w = 0; w < kRsWarps; w++) {
+            const uint32_t c = cnt[w][d];
+            cnt[w][d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int s = 0; s < kRsItems; s++) {
+        const int k = wbase + s * 32 + lane;
+        const uint32_t peers = __match_any_sync(0xffffffffu, dig[s]);
+        uint32_t pos = 0;
+        if (dig[s] != kRsNoDigit) pos = cnt[warp][dig[s]] + __popc(peers & ((1u << lane) - 1u));
+        __syncwarp();
+        if (dig[s] != kRsNoDigit && lane == __ffs(peers) - 1) cnt[warp][dig[s]] += __popc(peers);
+        __syncwarp();
+        if (dig[s] != kRsNoDigit) {
+            keys_out[pos] = key[s];
+            vals_out[pos] = vals_in[k];
+        }
+    }
+}
+
+// ---- K3a: Karras topology --------------------------------------------------
+// node ids: internal i in [0, n-2]; leaf k is encoded as ~k.  parent[] is
+// indexed by internal id for internal nodes and by (n-1)+k for leaves.
+__global__ void __launch_bounds__(kThreads)
+k_karras(int n, const uint64_t* __restrict__ keys, int2* __restrict__ children, int* __restrict__ parent) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int first, last, split;
+    karras_node(keys, n, i, first, last, split);
+    const int left = (split == first) ? ~split : split;
+    const int right = (split + 1 == last) ? ~(split + 1) : split + 1;
+    children[i] = make_int2(left, right);
+    parent[left >= 0 ? left : (n - 1) + ~left] = i;
+    parent[right >= 0 ? right : (n - 1) + ~right] = i;
+    if (i == 0) parent[0] = -1;
+}
+
+__device__ __forceinline__ Aabb leaf_box(const float3* __restrict__ wv, uint32_t prim, float pad) {
+    return aabb_pad(aabb_of_tri(wv[3 * prim], wv[3 * prim + 1], wv[3 * prim + 2]), pad);
+}
+
+// ---- K3b: bottom-up refit --------------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+k_refit(int n, const float3* __restrict__ wv, const uint32_t* __restrict__ order,
+        const int2* __restrict__ children, const int* __restrict__ parent, int* __restrict__ arrivals,
+        volatile float* node_box /* 6 floats per internal node */, float pad) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    int cur = parent[(n - 1) + k];
+    while (cur >= 0) {
+        __threadfence();
+        if (atomicAdd(&arrivals[cur], 1) == 0) return;  // sibling subtree not finished yet
+        __threadfence();
+        const int2 ch = children[cur];
+        Aabb b[2];
+#pragma unroll
+        for (int s = 0; s < 2; s++) {
+            const int c = s ? ch.y : ch.x;
+            if (c < 0) {
+                b[s] = leaf_box(wv, order[~c], pad);
+            } else {
+                volatile float* p = node_box + 6 * (size_t)c;
+                b[s].lo = v3(p[0], p[1], p[2]);
+                b[s].hi = v3(p[3], p[4], p[5]);
+            }
+        }
+        const Aabb u = aabb_union(b[0], b[1]);
+        volatile float* q = node_box + 6 * (size_t)cur;
+        q[0] = u.lo.x; q[1] = u.lo.y; q[2] = u.lo.z;
+        q[3] = u.hi.x; q[4] = u.hi.y; q[5] = u.hi.z;
+        cur = parent[cur];
+    }
+}
+
+// ---- K3c: emit traversal layout -------------------------------------------
+__global__ void __launch_bounds__(kThreads)
+k_emit_nodes(int n, const float3* __restrict__ wv, const uint32_t* __restrict__ order,
+             const int2* __restrict__ children, const float* __restrict__ node_box, float pad,
+             BvhNode2* __restrict__ nodes) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int2 ch = children[i];
+    Aabb b[2];
+#pragma unroll
+    for (int s = 0; s < 2; s++) {
+        const int c = s ? ch.y : ch.x;
+        if (c < 0) {
+            b[s] = leaf_box(wv, order[~c], pad);
+        } else {
+            const float* p = node_box + 6 * (size_t)c;
+            b[s].lo = v3(p[0], p[1], p[2]);
+            b[s].hi = v3(p[3], p[4], p[5]);
+        }
+    }
+    BvhNode2 nd;
+    nd.c0xy = make_float4(b[0].lo.x, b[0].hi.x, b[0].lo.y, b[0].hi.y);
+    nd.c1xy = make_float4(b[1].lo.x, b[1].hi.x, b[1].lo.y, b[1].hi.y);
+    nd.cz = make_float4(b[0].lo.z, b[0].hi.z, b[1].lo.z, b[1].hi.z);
+    nd.child0 = ch.x;
+    nd.child1 = ch.y;
+    nd.pad0 = nd.pad1 = 0;
+    nodes[i] = nd;
+}
+
+// single-triangle scene: one node, second child never hit
+__global__ void k_emit_single(const float3* __restrict__ wv, float pad, BvhNode2* __restrict__ nodes) {
+    const Aabb b = leaf_box(wv, 0, pad);
+    BvhNode2 nd;
+    nd.c0xy = make_float4(b.lo.x, b.hi.x, b.lo.y, b.hi.y);
+    nd.c1xy = make_float4(INFINITY, -INFINITY, INFINITY, -INFINITY);
+    nd.cz = make_float4(b.lo.z, b.hi.z, INFINITY, -INFINITY);
+    nd.child0 = ~0;
+    nd.child1 = ~0;
+    nd.pad0 = nd.pad1 = 0;
+    nodes[0] = nd;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_emit_tris(int n, const float3* __restrict__ wv, const float3* __restrict__ wn,
+            const uint32_t* __restrict__ order, const uint32_t* __restrict__ tri_mesh,
+            const MeshInfo* __restrict__ meshes, const int32_t* __restrict__ indices,
+            const float* __restrict__ texcoords, TriRecord* __restrict__ tris,
+            NrmRecord* __restrict__ nrms, UvRecord* __restrict__ uvs) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n) return;
+    const uint32_t g = order[s];
+    const uint32_t m = tri_mesh[g];
+    tris[s] = tri_pack(wv[3 * g], wv[3 * g + 1], wv[3 * g + 2], g, m);
+    const float3 n0 = wn[3 * g], n1 = wn[3 * g + 1], n2 = wn[3 * g + 2];
+    NrmRecord nr;
+    nr.a = make_float4(n0.x, n0.y, n0.z, n1.x);
+    nr.b = make_float4(n1.y, n1.z, n2.x, n2.y);
+    nr.c = make_float4(n2.z, __uint_as_float((uint32_t)meshes[m].has_normals), 0.0f, 0.0f);
+    nrms[s] = nr;
+    if (uvs) {
+        UvRecord ur;
+        ur.t0 = ur.t1 = ur.t2 = make_float2(0.0f, 0.0f);
+        const MeshInfo& mi = meshes[m];
+        if (mi.has_uv) {
+            const int i0 = indices[3 * g] + mi.vtx_offset, i1 = indices[3 * g + 1] + mi.vtx_offset,
+                      i2 = indices[3 * g + 2] + mi.vtx_offset;
+            ur.t0 = make_float2(texcoords[2 * i0], texcoords[2 * i0 + 1]);
+            ur.t1 = make_float2(texcoords[2 * i1], texcoords[2 * i1 + 1]);
+            ur.t2 = make_float2(texcoords[2 * i2], texcoords[2 * i2 + 1]);
+        }
+        uvs[s] = ur;
+    }
+}
+
+}  // namespace
+
+DeviceScene SceneBuffers::view() const {
+    DeviceScene s;
+    s.nodes = nodes.get();
+    s.tris = tris.get();
+    s.nrms = nrms.get();
+    s.uvs = uvs.get();
+    s.materials = materials.get();
+    s.textures = textures.get();
+    s.n_nodes = n_nodes;
+    s.n_tris = n_tris;
+    s.n_meshes = n_meshes;
+    s.n_textures = n_textures;
+    s.any_alpha_texture = any_alpha_texture;
+    return s;
+}
+
+int64_t SceneBuffers::device_bytes() const {
+    return (int64_t)(nodes.bytes() + tris.bytes() + nrms.bytes() + uvs.bytes() + materials.bytes() +
+                     textures.bytes() + tri_order.bytes());
+}
+
+void SceneBuffers::free_textures() {
+    for (auto t : texture_objects) cudaDestroyTextureObject(t);
+    for (auto a : texture_arrays) cudaFreeArray(a);
+    texture_objects.clear();
+    texture_arrays.clear();
+}
+
+// CreateTextures (OptixRenderer.cpp:562-612): uchar4 array, wrap, bilinear,
+// normalised float reads, normalised coordinates, sRGB = 0.
+static void create_textures(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stream) {
+    out.free_textures();
+    out.n_textures = desc.n_textures;
+    for (int i = 0; i < desc.n_textures; i++) {
+        const B2ptTexture& t = desc.textures[i];
+        B2PT_REQUIRE(t.rgba && t.width > 0 && t.height > 0, B2PT_E_INVALID, "texture with no pixels");
+        cudaChannelFormatDesc cd = cudaCreateChannelDesc<uchar4>();
+        cudaArray_t arr = nullptr;
+        B2PT_CUDA(cudaMallocArray(&arr, &cd, t.width, t.height));
+        out.texture_arrays.push_back(arr);
+        const size_t pitch = (size_t)t.width * 4;
+        B2PT_CUDA(cudaMemcpy2DToArray(arr, 0, 0, t.rgba, pitch, pitch, t.height, cudaMemcpyHostToDevice));
+        cudaResourceDesc rd = {};
+        rd.resType = cudaResourceTypeArray;
+        rd.res.array.array = arr;
+        cudaTextureDesc td = {};
+        td.addressMode[0] = td.addressMode[1] = cudaAddressModeWrap;
+        td.filterMode = cudaFilterModeLinear;
+        td.readMode = cudaReadModeNormalizedFloat;
+        td.normalizedCoords = 1;
+        td.maxAnisotropy = 1;
+        td.maxMipmapLevelClamp = 99;
+        td.minMipmapLevelClamp = 0;
+        td.mipmapFilterMode = cudaFilterModePoint;
+        td.borderColor[0] = 1.0f;
+        td.sRGB = 0;
+        cudaTextureObject_t obj = 0;
+        B2PT_CUDA(cudaCreateTextureObject(&obj, &rd, &td, nullptr));
+        out.texture_objects.push_back(obj);
+    }
+    out.textures.upload(out.texture_objects.data(), out.texture_objects.size(), stream);
+}
+
+void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stream) {
+    B2PT_REQUIRE(desc.n_meshes >= 0 && (desc.n_meshes == 0 || desc.meshes), B2PT_E_INVALID, "bad mesh array");
+    B2PT_REQUIRE(desc.n_textures >= 0 && (desc.n_textures == 0 || desc.textures), B2PT_E_INVALID,
+                 "bad texture array");
+
+    // ---- host: concatenate the per-mesh arrays (memcpy only) --------------
+    int64_t n_vtx = 0, n_tri = 0;
+    bool any_uv = false;
+    for (int m = 0; m < desc.n_meshes; m++) {
+        const B2ptMesh& me = desc.meshes[m];
+        B2PT_REQUIRE(me.n_vertices >= 0 && me.n_triangles >= 0, B2PT_E_INVALID, "negative mesh size");
+        B2PT_REQUIRE(me.n_triangles == 0 || (me.positions && me.indices), B2PT_E_INVALID,
+                     "mesh without positions/indices");
+        n_vtx += me.n_vertices;
+        n_tri += me.n_triangles;
+        any_uv |= me.texcoords != nullptr;
+    }
+    B2PT_REQUIRE(n_tri < (1ll << 30), B2PT_E_UNSUPPORTED, "more than 2^30 triangles");
+    std::vector<float> pos((size_t)n_vtx * 3), nrm((size_t)n_vtx * 3, 0.0f), uv(any_uv ? (size_t)n_vtx * 2 : 0, 0.0f);
+    std::vector<int32_t> idx((size_t)n_tri * 3);
+    std::vector<uint32_t> tri_mesh((size_t)n_tri);
+    std::vector<MeshInfo> infos((size_t)desc.n_meshes);
+    std::vector<MaterialRecord> mats((size_t)desc.n_meshes);
+    int64_t vo = 0, to = 0;
+    int any_alpha = 0;
+    for (int m = 0; m < desc.n_meshes; m++) {
+        const B2ptMesh& me = desc.meshes[m];
+        MeshInfo& mi = infos[m];
+        memcpy(mi.model, me.model, sizeof mi.model);
+        mi.vtx_offset = (int32_t)vo;
+        mi.tri_offset = (int32_t)to;
+        mi.has_normals = me.normals != nullptr;
+        mi.has_uv = me.texcoords != nullptr;
+        if (me.n_vertices) {
+            memcpy(&pos[vo * 3], me.positions, (size_t)me.n_vertices * 12);
+            if (me.normals) memcpy(&nrm[vo * 3], me.normals, (size_t)me.n_vertices * 12);
+            if (me.texcoords) memcpy(&uv[vo * 2], me.texcoords, (size_t)me.n_vertices * 8);
+        }
+        for (int64_t t = 0; t < me.n_triangles; t++) {
+            for (int k = 0; k < 3; k++) {
+                const int32_t v = me.indices[3 * t + k];
+                B2PT_REQUIRE(v >= 0 && v < me.n_vertices, B2PT_E_INVALID, "vertex index out of range");
+                idx[(to + t) * 3 + k] = v;
+            }
+            tri_mesh[to + t] = (uint32_t)m;
+        }
+        MaterialRecord& mr = mats[m];
+        mr.albedo[0] = me.albedo[0]; mr.albedo[1] = me.albedo[1]; mr.albedo[2] = me.albedo[2];
+        mr.metallic = me.metallic;
+        mr.roughness = me.roughness;
+        auto tex_ok = [&](int32_t t) { return (t >= 0 && t < desc.n_textures) ? t : -1; };
+        mr.tex_albedo = tex_ok(me.tex_albedo);
+        mr.tex_normal = tex_ok(me.tex_normal);
+        mr.tex_metal_rough = tex_ok(me.tex_metal_rough);
+        if (mr.tex_albedo >= 0 && me.texcoords) any_alpha = 1;
+        vo += me.n_vertices;
+        to += me.n_triangles;
+    }
+
+    const int n = (int)n_tri;
+    out.n_tris = n;
+    out.n_meshes = desc.n_meshes;
+    out.any_alpha_texture = any_alpha;
+    out.materials.upload(mats.data(), mats.size(), stream);
+    create_textures(desc, out, stream);
+    out.n_nodes = n == 0 ? 0 : (n == 1 ? 1 : n - 1);
+    out.nodes.alloc((size_t)out.n_nodes);
+    out.tris.alloc((size_t)n);
+    out.nrms.alloc((size_t)n);
+    out.uvs.alloc(any_uv ? (size_t)n : 0);
+    out.tri_order.alloc((size_t)n);
+    if (n == 0) {
+        B2PT_CUDA(cudaStreamSynchronize(stream));
+        return;
+    }
+
+    // ---- device: temporaries ----------------------------------------------
+    DeviceBuffer<float> d_pos, d_nrm, d_uv;
+    DeviceBuffer<int32_t> d_idx;
+    DeviceBuffer<uint32_t> d_tri_mesh, d_vals[2], d_hist;
+    DeviceBuffer<MeshInfo> d_infos;
+    DeviceBuffer<float3> d_wv, d_wn;
+    DeviceBuffer<uint64_t> d_keys[2];
+    DeviceBuffer<BoundsOrd> d_bounds;
+    DeviceBuffer<int2> d_children;
+    DeviceBuffer<int> d_parent, d_arrivals;
+    DeviceBuffer<float> d_node_box;
+    d_pos.upload(pos.data(), pos.size(), stream);
+    d_nrm.upload(nrm.data(), nrm.size(), stream);
+    if (any_uv) d_uv.upload(uv.data(), uv.size(), stream);
+    d_idx.upload(idx.data(), idx.size(), stream);
+    d_tri_mesh.upload(tri_mesh.data(), tri_mesh.size(), stream);
+    d_infos.upload(infos.data(), infos.size(), stream);
+    d_wv.alloc((size_t)n * 3);
+    d_wn.alloc((size_t)n * 3);
+    d_keys[0].alloc(n); d_keys[1].alloc(n);
+    d_vals[0].alloc(n); d_vals[1].alloc(n);
+    d_bounds.alloc(1);
+    const int n_tiles = (n + kRsTile - 1) / kRsTile;
+    d_hist.alloc((size_t)256 * n_tiles);
+    d_children.alloc(n > 1 ? n - 1 : 1);
+    d_parent.alloc((size_t)2 * n);
+    d_arrivals.alloc(n > 1 ? n - 1 : 1);
+    d_node_box.alloc((size_t)6 * (n > 1 ? n - 1 : 1));
+
+    cudaEvent_t ev0, ev1;
+    B2PT_CUDA(cudaEventCreate(&ev0));
+    B2PT_CUDA(cudaEventCreate(&ev1));
+    B2PT_CUDA(cudaEventRecord(ev0, stream));
+
+    k_init_bounds<<<1, 1, 0, stream>>>(d_bounds.get());
+    k_flatten<<<blocks_for(n), kThreads, 0, stream>>>(n, d_idx.get(), d_tri_mesh.get(), d_infos.get(),
+                                                       d_pos.get(), d_nrm.get(), d_wv.get(), d_wn.get(),
+                                                       d_bounds.get());
+    B2PT_CUDA(cudaGetLastError());
+    BoundsOrd hb;
+    d_bounds.download(&hb, 1, stream);
+    B2PT_CUDA(cudaStreamSynchronize(stream));
+    out.bounds_lo = v3(ord2f(hb.vlo[0]), ord2f(hb.vlo[1]), ord2f(hb.vlo[2]));
+    out.bounds_hi = v3(ord2f(hb.vhi[0]), ord2f(hb.vhi[1]), ord2f(hb.vhi[2]));
+    float maxabs = 0.0f;
+    for (int i = 0; i < 3; i++) {
+        maxabs = fmaxf(maxabs, fabsf(ord2f(hb.vlo[i])));
+        maxabs = fmaxf(maxabs, fabsf(ord2f(hb.vhi[i])));
+    }
+    B2PT_REQUIRE(std::isfinite(maxabs), B2PT_E_INVALID, "non-finite vertex positions");
+    // outward box padding: 2^-18 of the largest coordinate (see traverse.cuh)
+    const float pad = fmaxf(maxabs, 1e-30f) * 3.8146973e-6f;
+
+    k_morton<<<blocks_for(n), kThreads, 0, stream>>>(n, d_wv.get(), d_bounds.get(), d_keys[0].get(),
+                                                      d_vals[0].get());
+    int cur = 0;
+    for (int pass = 0; pass < 8; pass++) {
+        const int shift = pass * 8;
+        k_rs_hist<<<n_tiles, kRsWarps * 32, 0, stream>>>(n, d_keys[cur].get(), shift, n_tiles, d_hist.get());
+        k_rs_scan<<<1, 1024, 0, stream>>>(256 * n_tiles, d_hist.get());
+        k_rs_scatter<<<n_tiles, kRsWarps * 32, 0, stream>>>(n, d_keys[cur].get(), d_vals[cur].get(),
+                                                            d_keys[cur ^ 1].get(), d_vals[cur ^ 1].get(),
+                                                            shift, n_tiles, d_hist.get());
+        cur ^= 1;
+    }
+    B2PT_CUDA(cudaGetLastError());
+    const uint64_t* keys = d_keys[cur].get();
+    const uint32_t* order = d_vals[cur].get();
+
+    if (n > 1) {
+        d_arrivals.zero(stream);
+        k_karras<<<blocks_for(n - 1), kThreads, 0, stream>>>(n, keys, d_children.get(), d_parent.get());
+        k_refit<<<blocks_for(n), kThreads, 0, stream>>>(n, d_wv.get(), order, d_children.get(),
+                                                         d_parent.get(), d_arrivals.get(),
+                                                         d_node_box.get(), pad);
+        k_emit_nodes<<<blocks_for(n - 1), kThreads, 0, stream>>>(n, d_wv.get(), order, d_children.get(),
+                                                                  d_node_box.get(), pad, out.nodes.get());
+    } else {
+        k_emit_single<<<1, 1, 0, stream>>>(d_wv.get(), pad, out.nodes.get());
+    }
+    k_emit_tris<<<blocks_for(n), kThreads, 0, stream>>>(n, d_wv.get(), d_wn.get(), order, d_tri_mesh.get(),
+                                                         d_infos.get(), d_idx.get(), d_uv.get(),
+                                                         out.tris.get(), out.nrms.get(), out.uvs.get());
+    B2PT_CUDA(cudaGetLastError());
+    B2PT_CUDA(cudaMemcpyAsync(out.tri_order.get(), order, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
+    B2PT_CUDA(cudaEventRecord(ev1, stream));
+    B2PT_CUDA(cudaStreamSynchronize(stream));
+    B2PT_CUDA(cudaEventElapsedTime(&out.build_ms, ev0, ev1));
+    cudaEventDestroy(ev0);
+    cudaEventDestroy(ev1);
+}
+
+}  // namespace b2pt

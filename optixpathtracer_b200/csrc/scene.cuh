@@ -1,0 +1,76 @@
+// scene.cuh — flattened device scene (what kernels see) and the build entry.
+//
+// The reference keeps one set of device arrays per mesh and reaches them per
+// hit through the SBT record (MeshSBTData.h:6-29, filled in
+// OptixRenderer.cpp:520-554): record -> index[prim] -> 3 x vertex / normal /
+// texcoord, each vertex re-multiplied by modelMatrix in the closest-hit program
+// (devicePrograms.cu:77-81).  Here everything is pre-transformed once and laid
+// out per triangle in leaf order, so a hit costs 3+3 coalescable 16-byte loads
+// and no matrix work.
+#pragma once
+
+#include <vector>
+
+#include "bvh.cuh"
+#include "host_util.h"
+
+namespace b2pt {
+
+// per-mesh material constants: MeshSBTData.albedoColor/roughness/metallic +
+// texture ids (Mesh.h:29-37).  32 bytes, two LDG.128.
+struct alignas(16) MaterialRecord {
+    float albedo[3];
+    float metallic;
+    float roughness;
+    int32_t tex_albedo;   // < 0: none
+    int32_t tex_normal;
+    int32_t tex_metal_rough;
+};
+static_assert(sizeof(MaterialRecord) == 32, "material record must be 32 bytes");
+
+struct MeshInfo {
+    float model[16];  // column-major
+    int32_t vtx_offset;
+    int32_t tri_offset;
+    int32_t has_normals;
+    int32_t has_uv;
+};
+
+// POD view handed to kernels by value.
+struct DeviceScene {
+    const BvhNode2* nodes;
+    const TriRecord* tris;
+    const NrmRecord* nrms;
+    const UvRecord* uvs;            // nullptr when no mesh has texcoords
+    const MaterialRecord* materials;
+    const cudaTextureObject_t* textures;
+    int32_t n_nodes;
+    int32_t n_tris;
+    int32_t n_meshes;
+    int32_t n_textures;
+    int32_t any_alpha_texture;      // some mesh has an albedo texture (any-hit cut-out, A9)
+};
+
+struct SceneBuffers {
+    DeviceBuffer<BvhNode2> nodes;
+    DeviceBuffer<TriRecord> tris;
+    DeviceBuffer<NrmRecord> nrms;
+    DeviceBuffer<UvRecord> uvs;
+    DeviceBuffer<MaterialRecord> materials;
+    DeviceBuffer<cudaTextureObject_t> textures;
+    DeviceBuffer<uint32_t> tri_order;   // leaf slot -> global primitive id
+    std::vector<cudaArray_t> texture_arrays;
+    std::vector<cudaTextureObject_t> texture_objects;
+    int32_t n_tris = 0, n_nodes = 0, n_meshes = 0, n_textures = 0, any_alpha_texture = 0;
+    float build_ms = 0.0f;
+    float3 bounds_lo = {0, 0, 0}, bounds_hi = {0, 0, 0};
+
+    DeviceScene view() const;
+    int64_t device_bytes() const;
+    void free_textures();
+};
+
+// Upload + flatten + LBVH build (K1-K3) on `stream`.  Throws b2pt::Error.
+void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stream);
+
+}  // namespace b2pt

@@ -1,0 +1,78 @@
+// wavefront.cuh — data layout of the wavefront integrator and kernel launchers.
+//
+// The reference is an OptiX megakernel: one thread per pixel runs the whole
+// path loop (devicePrograms.cu:625-664) with its state in a 64-byte
+// RadianceRayData reached through two payload registers (RayData.h:5-51), and
+// closest-hit does all shading plus a nested shadow trace (:343-514).
+// Here the path loop is unrolled in time: every bounce is a short sequence of
+// kernels over structure-of-arrays path state, so each kernel is coherent
+// (traversal only traverses, each BSDF kernel only evaluates one BSDF) and
+// every global access of the state is coalesced.
+//
+// Per bounce:   K5 closest-hit  ->  K6 surface + classify + light pick
+//            -> K8 shadow any-hit -> K7a..d shade (NEE add, sample, next ray,
+//               termination, compaction into the other state buffer)
+// Per wave:     K4 raygen before the first bounce, K9 accumulate after the last.
+#pragma once
+
+#include "scene.cuh"
+
+namespace b2pt {
+
+// SoA path state; one slot per in-flight path.  Two copies (ping-pong): the
+// shade kernels write survivors densely into the other copy (A3 in SURVEY §8).
+struct PathState {
+    float *ox, *oy, *oz;      // next ray origin      (RadianceRayData.nextOrigin)
+    float *dx, *dy, *dz;      // next ray direction   (.nextDirection)
+    float *bx, *by, *bz;      // throughput           (.beta)
+    float *rx, *ry, *rz;      // radiance so far      (.radiance)
+    uint32_t* id;             // pixel + W*H*local_sample: where the result goes
+    uint32_t* seed;           // LCG state (.randomSeed); unused with Philox
+};
+constexpr int kPathStateWords = 14;
+
+// Per-hit record written by K6 and read by K7 (Surface.h:5-39, minus what can
+// be recomputed from it): 56 bytes, SoA.
+struct SurfaceState {
+    float *px, *py, *pz;      // surface.position
+    float *gx, *gy, *gz;      // surface.gNormal (world)
+    float *nx, *ny, *nz;      // surface.sNormal (world); the shading frame is rebuilt from it
+    float *ar, *ag, *ab;      // surface.albedo
+    float* rough;             // surface.roughness
+    uint32_t* info;           // bits 0-7 light index, 8 has-light, 9 conductor, 10 visible (set by K8)
+};
+constexpr int kSurfaceStateWords = 14;
+constexpr uint32_t kInfoHasLight = 1u << 8;
+constexpr uint32_t kInfoConductor = 1u << 9;
+constexpr uint32_t kInfoVisible = 1u << 10;
+
+// Shadow rays, one per slot (LightVisibility, devicePrograms.cu:216-241).
+struct ShadowRays {
+    float *ox, *oy, *oz, *dx, *dy, *dz;
+    float* tmax;              // < 0: no shadow ray for this slot
+};
+constexpr int kShadowWords = 7;
+
+struct TraceCounters {
+    unsigned long long nodes, tris, exact, radiance_rays, shadow_rays, nan_samples;
+};
+
+// ---- launchers (wavefront.cu / trace_kernels.cu) ---------------------------
+struct LaunchCfg {
+    cudaStream_t stream;
+    int grid;            // persistent grid: multiple of the SM count
+    bool stats;
+    uint64_t* launch_counter;
+};
+
+// K5: closest hit for rays [0, *n_active) of `st`; n_active lives on the device.
+void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState& st,
+                    const uint32_t* n_active, float tmin, float tmax, HitRecord* hits,
+                    TraceCounters* counters);
+// K8: any hit for shadow rays [0, *n_active); sets kInfoVisible in info[] (if
+// info != nullptr) and/or occluded[] (if non-null).
+void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh,
+                const uint32_t* n_active, float tmin, uint32_t* info, uint8_t* occluded,
+                TraceCounters* counters);
+
+}  // namespace b2pt

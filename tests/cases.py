@@ -1,0 +1,68 @@
+"""Seeded ray/scene cases shared by the CPU-tier and GPU-tier traversal tests."""
+from __future__ import annotations
+
+import numpy as np
+
+from optixpathtracer_b200 import camera_rays, scenes
+
+f32 = np.float32
+
+
+def small_spheres(segments=24, rings=12):
+    return scenes.spheres_scene(segments=segments, rings=rings)
+
+
+def scene_rays(scene, w, h, n_random, seed):
+    """Primary rays of the scene camera + random interior rays + axis-parallel rays."""
+    pos, iv, ip = scene["camera"].launch_matrices(w, h)
+    o, d = camera_rays(pos, iv, ip, w, h)
+    rng = np.random.default_rng(seed)
+    o2 = rng.uniform([-0.5, -0.5, -2.0], [3.0, 2.5, 2.0], (n_random, 3)).astype(f32)
+    d2 = rng.normal(size=(n_random, 3))
+    d2 = (d2 / np.linalg.norm(d2, axis=1, keepdims=True)).astype(f32)
+    # rays with exact zero direction components (slab test edge case)
+    axes = np.array([[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, -1, 0], [0, 0, 1], [0, 0, -1],
+                     [0.6, 0.8, 0], [0, 0.6, -0.8]], dtype=f32)
+    o3 = rng.uniform([0.5, 0.0, -1.5], [3.0, 2.0, 1.5], (len(axes) * 40, 3)).astype(f32)
+    d3 = np.tile(axes, (40, 1))
+    return np.concatenate([o, o2, o3]), np.concatenate([d, d2, d3])
+
+
+def edge_soup():
+    """Hand-made soup exercising ties, shared edges, degenerate and tiny triangles."""
+    t = []
+    # two coplanar triangles sharing the diagonal of a unit quad at z = 0
+    t.append([[0, 0, 0], [1, 0, 0], [1, 1, 0]])
+    t.append([[0, 0, 0], [1, 1, 0], [0, 1, 0]])
+    # an exact duplicate of triangle 0 (tie on t: lower primitive id must win)
+    t.append([[0, 0, 0], [1, 0, 0], [1, 1, 0]])
+    # a degenerate (zero-area) triangle
+    t.append([[0.2, 0.2, 0.5], [0.4, 0.4, 0.5], [0.6, 0.6, 0.5]])
+    # a tiny triangle far from the origin
+    t.append([[50, 50, 50], [50.001, 50, 50], [50, 50.001, 50]])
+    # back-facing quad at z = -1 (opposite winding)
+    t.append([[0, 0, -1], [1, 1, -1], [1, 0, -1]])
+    t.append([[0, 0, -1], [0, 1, -1], [1, 1, -1]])
+    return np.array(t, dtype=f32)
+
+
+def edge_rays():
+    o, d = [], []
+    # through the shared diagonal, vertices, and edges of the quad at z=0
+    for x, y in [(0.5, 0.5), (0.25, 0.25), (0.0, 0.0), (1.0, 1.0), (1.0, 0.0), (0.5, 0.0),
+                 (0.0, 0.5), (0.3, 0.7), (0.7, 0.3), (1.0, 0.5), (0.5, 1.0), (1.5, 0.5), (-0.1, 0.2)]:
+        o.append([x, y, 2.0]); d.append([0, 0, -1])
+        o.append([x, y, -3.0]); d.append([0, 0, 1])
+    # grazing, parallel to the plane
+    o.append([-1, 0.5, 0.0]); d.append([1, 0, 0])
+    o.append([-1, 0.5, 1e-7]); d.append([1, 0, 0])
+    # origin exactly on the surface (t = 0 must not count)
+    o.append([0.5, 0.25, 0.0]); d.append([0, 0, -1])
+    o.append([0.5, 0.25, 0.0]); d.append([0, 0, 1])
+    # towards the tiny far triangle
+    o.append([0, 0, 0]); d.append([50.0003, 50.0003, 50])
+    o.append([50.0003, 50.0003, 60]); d.append([0, 0, -1])
+    o = np.array(o, dtype=f32)
+    d = np.array(d, dtype=f32)
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(f32)
+    return o, d

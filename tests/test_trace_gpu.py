@@ -1,0 +1,147 @@
+"""GPU tier: K1-K3 (LBVH build) + K5/K8 (traversal) against the oracle.
+
+Everything goes through the C-ABI (b2pt_create / b2pt_trace_closest /
+b2pt_trace_any).  Bar: primitive ids, t, u, v bit-exact; occlusion exact.
+"""
+import numpy as np
+import pytest
+
+from tests import cases
+from tests.util import bits, random_rays
+from optixpathtracer_b200 import scenes
+
+pytestmark = pytest.mark.gpu
+f32 = np.float32
+
+
+def _renderer(scene, **kw):
+    from optixpathtracer_b200 import OptixRenderer
+    return OptixRenderer(None, scene, **kw)
+
+
+def _soup_scene(soup):
+    soup = np.asarray(soup, dtype=f32).reshape(-1, 3, 3)
+    return {"meshes": [{"positions": soup.reshape(-1, 3), "normals": None, "texcoords": None,
+                        "indices": np.arange(len(soup) * 3, dtype=np.int32).reshape(-1, 3),
+                        "model": np.eye(4, dtype=f32), "albedo": (1, 1, 1), "metallic": 0.0,
+                        "roughness": 0.5}] if len(soup) else [], "textures": []}
+
+
+def _compare(r, oracle, soup, o, d, tmin=0.0, tmax=100.0):
+    gp, gm, gt, gu, gv = r.TraceClosest(o, d, tmin, tmax)
+    op, ot, ou, ov, obf = oracle.closest(soup, o, d, tmin, tmax)
+    assert np.array_equal(gp, op), f"{(gp != op).sum()} primitive ids differ"
+    assert np.array_equal(bits(gt), bits(ot))
+    assert np.array_equal(bits(gu), bits(ou))
+    assert np.array_equal(bits(gv), bits(ov))
+    return op, ot, gm
+
+
+def test_bvh_structure():
+    sc = cases.small_spheres()
+    with _renderer(sc) as r:
+        st = r.Stats()
+        nt = st["n_triangles"]
+        assert nt == sum(len(m["indices"]) for m in sc["meshes"])
+        assert st["n_nodes"] == nt - 1 and st["node_bytes"] == 64 and st["triangle_bytes"] == 48
+        nodes, order = r.DownloadBvh()
+        assert sorted(order.tolist()) == list(range(nt))          # a permutation
+        child = nodes.view(np.int32)[:, 12:14]
+        seen = np.zeros(nt, dtype=np.int32)
+        visited = 0
+        stack = [0]
+        while stack:
+            c = stack.pop()
+            if c < 0:
+                seen[~c] += 1
+                continue
+            visited += 1
+            stack += [int(child[c, 0]), int(child[c, 1])]
+        assert visited == nt - 1 and (seen == 1).all()
+        # child boxes contain their subtree's triangles: check the root's two boxes cover the scene
+        soup, _ = scenes.scene_triangle_soup(sc)
+        lo = soup.reshape(-1, 3).min(0)
+        hi = soup.reshape(-1, 3).max(0)
+        root = nodes[0]
+        blo = np.array([min(root[0], root[4]), min(root[2], root[6]), min(root[8], root[10])])
+        bhi = np.array([max(root[1], root[5]), max(root[3], root[7]), max(root[9], root[11])])
+        assert (blo <= lo).all() and (bhi >= hi).all()
+
+
+def test_scene1_closest_and_any(oracle):
+    sc = cases.small_spheres()
+    soup, mesh_ids = scenes.scene_triangle_soup(sc)
+    o, d = cases.scene_rays(sc, 96, 64, 6000, seed=5)
+    with _renderer(sc) as r:
+        prim, t, gm = _compare(r, oracle, soup, o, d)
+        hit = prim >= 0
+        assert np.array_equal(gm[hit], mesh_ids[prim[hit]]) and (gm[~hit] == -1).all()
+        tm = np.where(hit, t * np.where(np.arange(len(t)) % 2 == 0, f32(0.999), f32(1.001)), f32(5.0)).astype(f32)
+        assert np.array_equal(r.TraceAny(o, d, tm), oracle.any(soup, o, d, tm))
+        _compare(r, oracle, soup, o, d, tmin=1.0, tmax=4.0)
+
+
+def test_edge_cases(oracle):
+    soup = cases.edge_soup()
+    o, d = cases.edge_rays()
+    with _renderer(_soup_scene(soup)) as r:
+        _compare(r, oracle, soup, o, d)
+        _compare(r, oracle, soup, o, d, tmin=0.5, tmax=2.5)
+        assert np.array_equal(r.TraceAny(o, d, 100.0), oracle.any(soup, o, d, 100.0))
+
+
+def test_tiny_and_empty_scenes(oracle):
+    rng = np.random.default_rng(3)
+    o, d = random_rays(rng, 500, [-2, -2, -2], [2, 2, 2])
+    for nt in (1, 2, 3, 7):
+        soup = rng.uniform(-1, 1, (nt, 3, 3)).astype(f32)
+        with _renderer(_soup_scene(soup)) as r:
+            _compare(r, oracle, soup, o, d)
+    with _renderer(_soup_scene(np.zeros((0, 3, 3)))) as r:
+        prim, *_ = r.TraceClosest(o, d)
+        assert (prim == -1).all()
+        assert (r.TraceAny(o, d, 10.0) == 0).all()
+        assert r.Stats()["n_nodes"] == 0
+
+
+def test_far_origins_small_triangles(oracle):
+    rng = np.random.default_rng(11)
+    c = rng.uniform(-1, 1, (4000, 1, 3))
+    soup = (c + rng.normal(scale=0.01, size=(4000, 3, 3))).astype(f32)
+    tgt = soup.reshape(-1, 3)[rng.integers(0, 12000, 4000)]
+    o = (tgt + rng.normal(size=(4000, 3)) * 30).astype(f32)
+    d = tgt - o
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(f32)
+    with _renderer(_soup_scene(soup)) as r:
+        _compare(r, oracle, soup, o, d, 0.0, 1000.0)
+
+
+def test_model_matrix_and_mesh_offsets(oracle):
+    """Several meshes with non-trivial transforms: the GPU flatten (k_flatten)
+    must produce the same fp32 world-space soup as the numpy statement."""
+    rng = np.random.default_rng(21)
+    meshes = []
+    for k in range(5):
+        pos = rng.uniform(-1, 1, (30, 3)).astype(f32)
+        idx = rng.integers(0, 30, (40, 3)).astype(np.int32)
+        M = np.eye(4, dtype=f32)
+        M[:3, :3] = (np.linalg.qr(rng.normal(size=(3, 3)))[0] * rng.uniform(0.3, 2.0)).astype(f32)
+        M[:3, 3] = rng.uniform(-2, 2, 3)
+        meshes.append({"positions": pos, "normals": None, "texcoords": None, "indices": idx,
+                       "model": M, "albedo": (1, 1, 1), "metallic": 0.0, "roughness": 0.5})
+    sc = {"meshes": meshes, "textures": []}
+    soup, _ = scenes.scene_triangle_soup(sc)
+    o, d = random_rays(rng, 4000, [-4, -4, -4], [4, 4, 4])
+    with _renderer(sc) as r:
+        _compare(r, oracle, soup, o, d)
+
+
+def test_stats_counters():
+    sc = cases.small_spheres()
+    o, d = cases.scene_rays(sc, 64, 64, 0, seed=1)
+    with _renderer(sc, collect_stats=True) as r:
+        r.TraceClosest(o, d)
+        st = r.Stats()
+        assert st["radiance_rays"] == len(o)
+        assert st["nodes_visited"] > len(o) and st["triangles_tested"] > 0
+        assert st["exact_tests"] <= st["triangles_tested"]
