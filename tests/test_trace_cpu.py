@@ -99,3 +99,26 @@ def test_traversal_logic_random_soup_far_origins(hostsim, oracle):
     d = tgt - o
     d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(f32)
     _compare(hostsim, oracle, soup, o, d, 0.0, 1000.0)
+
+
+def test_host_bvh_equals_bruteforce(oracle):
+    """oracle/host_bvh.h (used to make the CPU oracle render in finite time) must
+    return exactly what the exhaustive search returns."""
+    import ctypes as C
+    from tests.util import fp, vp
+    sc = cases.small_spheres()
+    soup, _ = scenes.scene_triangle_soup(sc)
+    o, d = cases.scene_rays(sc, 48, 32, 2000, seed=9)
+    n = len(o)
+    op, ot, ou, ov, obf = oracle.closest(soup, o, d)
+    prim = np.empty(n, np.int32); t = np.empty(n, f32); u = np.empty(n, f32); v = np.empty(n, f32)
+    bf = np.empty(n, np.uint8)
+    s9 = np.ascontiguousarray(soup.reshape(-1, 9))
+    oracle.lib.oracle_closest_bvh(fp(s9), C.c_int64(len(s9)), fp(o), fp(d), C.c_int64(n), C.c_float(0),
+                                  C.c_float(100), vp(prim), fp(t), fp(u), fp(v), vp(bf))
+    assert np.array_equal(prim, op) and np.array_equal(bits(t), bits(ot))
+    assert np.array_equal(bits(u), bits(ou)) and np.array_equal(bits(v), bits(ov)) and np.array_equal(bf, obf)
+    tm = np.where(op >= 0, ot * f32(0.999), f32(3.0)).astype(f32)
+    occ = np.empty(n, np.uint8)
+    oracle.lib.oracle_any_bvh(fp(s9), C.c_int64(len(s9)), fp(o), fp(d), C.c_int64(n), C.c_float(0), fp(tm), vp(occ))
+    assert np.array_equal(occ, oracle.any(soup, o, d, tm))
