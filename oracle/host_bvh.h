@@ -48,7 +48,20 @@ class HostBvh {
         }
     }
 
+    struct AcceptAll {
+        bool operator()(int64_t, double, double) const { return true; }
+    };
     ClosestHit closest(const float* o, const float* d, double tmin, double tmax) const {
+        return closest(o, d, tmin, tmax, AcceptAll());
+    }
+    bool any(const float* o, const float* d, double tmin, double tmax) const {
+        return any(o, d, tmin, tmax, AcceptAll());
+    }
+
+    // `accept(prim, u, v)` plays the any-hit program: returning false ignores
+    // the intersection (optixIgnoreIntersection, devicePrograms.cu:549-561).
+    template <class Accept>
+    ClosestHit closest(const float* o, const float* d, double tmin, double tmax, const Accept& accept) const {
         ClosestHit best;
         if (nodes_.empty()) return best;
         double bt = tmax;
@@ -65,6 +78,7 @@ class HostBvh {
                     const Hit h = exact_triangle(o, d, tris_ + 9 * p);
                     if (!h.hit || !(h.t > tmin) || !(h.t < tmax)) continue;
                     if (h.t < bt || (h.t == bt && best.prim >= 0 && p < best.prim)) {
+                        if (!accept(p, h.u, h.v)) continue;
                         bt = h.t;
                         best.prim = p; best.t = h.t; best.u = h.u; best.v = h.v; best.backface = h.backface;
                     }
@@ -77,7 +91,8 @@ class HostBvh {
         return best;
     }
 
-    bool any(const float* o, const float* d, double tmin, double tmax) const {
+    template <class Accept>
+    bool any(const float* o, const float* d, double tmin, double tmax, const Accept& accept) const {
         if (nodes_.empty()) return false;
         const double inv[3] = {1.0 / safe(d[0]), 1.0 / safe(d[1]), 1.0 / safe(d[2])};
         int stack[128];
@@ -89,7 +104,7 @@ class HostBvh {
             if (nd.count) {
                 for (int64_t k = nd.first; k < nd.first + nd.count; k++) {
                     const Hit h = exact_triangle(o, d, tris_ + 9 * order_[k]);
-                    if (h.hit && h.t > tmin && h.t < tmax) return true;
+                    if (h.hit && h.t > tmin && h.t < tmax && accept(order_[k], h.u, h.v)) return true;
                 }
             } else {
                 stack[sp++] = nd.left;

@@ -128,3 +128,99 @@ def random_rays(rng, n, lo, hi):
     d = rng.normal(size=(n, 3))
     d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(f32)
     return o, d
+
+
+class RefOracle:
+    """oracle/_ref/liboracle_ref.so: the reference's own device code compiled for
+    the host (oracle/ref_harness.cpp).  Takes the same scene dicts / B2ptSceneDesc
+    as the product."""
+
+    PATH = ROOT / "oracle" / "_ref" / "liboracle_ref.so"
+
+    @classmethod
+    def available(cls) -> bool:
+        return cls.PATH.exists()
+
+    def __init__(self):
+        self.lib = C.CDLL(str(self.PATH))
+        self.lib.ref_scene_create.restype = C.c_void_p
+        self.lib.ref_scene_triangles.restype = C.c_int64
+        self.lib.ref_tea16.restype = C.c_uint32
+        self.lib.ref_rnd.restype = C.c_float
+
+    # -- BSDF level ---------------------------------------------------------
+    @staticmethod
+    def _prep(n, albedo, roughness):
+        a = np.ascontiguousarray(np.broadcast_to(np.asarray(albedo, dtype=f32), (n, 3)), dtype=f32)
+        r = np.ascontiguousarray(np.broadcast_to(np.asarray(roughness, dtype=f32), (n,)), dtype=f32)
+        return a, r
+
+    def bsdf_f(self, bsdf, albedo, roughness, wo, wi, seed=None):
+        wo = np.ascontiguousarray(wo, dtype=f32).reshape(-1, 3)
+        wi = np.ascontiguousarray(wi, dtype=f32).reshape(-1, 3)
+        n = len(wo)
+        a, r = self._prep(n, albedo, roughness)
+        sd = np.ascontiguousarray(np.broadcast_to(np.asarray(0 if seed is None else seed, dtype=np.uint32), (n,)), dtype=np.uint32)
+        out = np.empty((n, 3), f32)
+        so = np.empty(n, np.uint32)
+        self.lib.ref_bsdf_f(C.c_int(bsdf), C.c_int64(n), fp(a), fp(r), fp(wo), fp(wi), vp(sd), fp(out), vp(so))
+        return out, so
+
+    def bsdf_sample(self, bsdf, albedo, roughness, wo, seed):
+        wo = np.ascontiguousarray(wo, dtype=f32).reshape(-1, 3)
+        n = len(wo)
+        a, r = self._prep(n, albedo, roughness)
+        sd = np.ascontiguousarray(np.broadcast_to(np.asarray(seed, dtype=np.uint32), (n,)), dtype=np.uint32)
+        ok = np.empty(n, np.uint8)
+        f = np.empty((n, 3), f32)
+        wi = np.empty((n, 3), f32)
+        pdf = np.empty(n, f32)
+        flags = np.empty(n, np.uint8)
+        so = np.empty(n, np.uint32)
+        self.lib.ref_bsdf_sample(C.c_int(bsdf), C.c_int64(n), fp(a), fp(r), fp(wo), vp(sd), vp(ok), fp(f), fp(wi),
+                                 fp(pdf), vp(flags), vp(so))
+        return ok, f, wi, pdf, flags, so
+
+    def bsdf_pdf(self, bsdf, roughness, wo, wi, reflection=True, transmission=True):
+        wo = np.ascontiguousarray(wo, dtype=f32).reshape(-1, 3)
+        wi = np.ascontiguousarray(wi, dtype=f32).reshape(-1, 3)
+        n = len(wo)
+        _, r = self._prep(n, (1, 1, 1), roughness)
+        out = np.empty(n, f32)
+        self.lib.ref_bsdf_pdf(C.c_int(bsdf), C.c_int64(n), fp(r), fp(wo), fp(wi), C.c_int(int(reflection)),
+                              C.c_int(int(transmission)), fp(out))
+        return out
+
+    # -- frame level --------------------------------------------------------
+    def render(self, scene, width, height, *, bsdf_mode=0, max_bounces=8, frame_first=1, n_frames=1,
+               lights=None, restated=False, want_frames=False):
+        """Returns (running mean (H,W,3), frames (n,H,W,3) | None, counters dict)."""
+        from optixpathtracer_b200.api import _SceneMarshal
+        from optixpathtracer_b200._lib import B2ptPointLight
+        m = _SceneMarshal(scene)
+        h = C.c_void_p(self.lib.ref_scene_create(C.byref(m.desc)))
+        try:
+            pos, iv, ip = scene["camera"].launch_matrices(width, height)
+            lights = scene["lights"] if lights is None else lights
+            arr = (B2ptPointLight * max(len(lights), 1))()
+            for i, (p, c) in enumerate(lights):
+                arr[i].position = (C.c_float * 3)(*np.asarray(p, dtype=f32))
+                arr[i].color = (C.c_float * 3)(*np.asarray(c, dtype=f32))
+            mean = np.empty((height, width, 3), f32)
+            frames = np.empty((n_frames, height, width, 3), f32) if want_frames else None
+            cnt = (C.c_uint64 * 4)()
+            self.lib.ref_render(h, C.c_int(width), C.c_int(height), fp(pos), fp(iv), fp(ip), arr,
+                                C.c_int(len(lights)), C.c_int(max_bounces), C.c_int(bsdf_mode),
+                                C.c_int(int(restated)), C.c_uint32(frame_first), C.c_int(n_frames), fp(mean),
+                                fp(frames) if want_frames else None, cnt)
+        finally:
+            self.lib.ref_scene_destroy(h)
+        return mean, frames, {"radiance_rays": cnt[0], "shadow_rays": cnt[1], "nan_samples": cnt[2],
+                              "threads": cnt[3]}
+
+    def camera_rays(self, camera, width, height):
+        pos, iv, ip = camera.launch_matrices(width, height)
+        o = np.empty((width * height, 3), f32)
+        d = np.empty((width * height, 3), f32)
+        self.lib.ref_camera_rays(C.c_int(width), C.c_int(height), fp(pos), fp(iv), fp(ip), fp(o), fp(d))
+        return o, d
