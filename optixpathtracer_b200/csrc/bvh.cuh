@@ -13,7 +13,7 @@
 //   one node fetch decides both children (Aila-Laine layout).
 //   TriRecord (48 B, 3 x LDG.128): world-space v0,v1,v2 + global primitive id,
 //   stored in leaf (Morton) order.
-//   NrmRecord (48 B): world-space vertex normals + mesh id, same order.
+//   NrmRecord (48 B): object-space vertex normals + has-normals flag, same order.
 #pragma once
 
 #include "vecmath.cuh"
@@ -38,7 +38,8 @@ struct alignas(16) TriRecord {
 static_assert(sizeof(TriRecord) == 48, "triangle record must be 48 bytes");
 
 struct alignas(16) NrmRecord {
-    float4 a;   // n0.x n0.y n0.z n1.x      (world space: M * (n,0), not normalised)
+    float4 a;   // n0.x n0.y n0.z n1.x      (OBJECT space, as uploaded: the reference
+                //  interpolates first and transforms after, devicePrograms.cu:95-100)
     float4 b;   // n1.y n1.z n2.x n2.y
     float4 c;   // n2.z, has_normals (bits), unused, unused
 };

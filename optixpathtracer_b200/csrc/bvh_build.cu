@@ -57,8 +57,7 @@ __global__ void k_init_bounds(BoundsOrd* b) {
 __global__ void __launch_bounds__(kThreads)
 k_flatten(int n_tris, const int32_t* __restrict__ indices, const uint32_t* __restrict__ tri_mesh,
           const MeshInfo* __restrict__ meshes, const float* __restrict__ positions,
-          const float* __restrict__ normals, float3* __restrict__ wv, float3* __restrict__ wn,
-          BoundsOrd* bounds) {
+          float3* __restrict__ wv, BoundsOrd* bounds) {
     const int g = blockIdx.x * blockDim.x + threadIdx.x;
     float3 clo = v3(INFINITY), chi = v3(-INFINITY), vlo = v3(INFINITY), vhi = v3(-INFINITY);
     if (g < n_tris) {
@@ -70,12 +69,6 @@ k_flatten(int n_tris, const int32_t* __restrict__ indices, const uint32_t* __res
             const float4 w = mat4_mul(mi.model, positions[3 * vi], positions[3 * vi + 1], positions[3 * vi + 2], 1.0f);
             p[k] = v3(w.x, w.y, w.z);
             wv[3 * g + k] = p[k];
-            float3 nw = v3(0.0f);
-            if (mi.has_normals) {
-                const float4 t = mat4_mul(mi.model, normals[3 * vi], normals[3 * vi + 1], normals[3 * vi + 2], 0.0f);
-                nw = v3(t.x, t.y, t.z);
-            }
-            wn[3 * g + k] = nw;
         }
         const Aabb bb = aabb_of_tri(p[0], p[1], p[2]);
         vlo = bb.lo;
@@ -310,7 +303,7 @@ __global__ void k_emit_single(const float3* __restrict__ wv, float pad, BvhNode2
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_emit_tris(int n, const float3* __restrict__ wv, const float3* __restrict__ wn,
+k_emit_tris(int n, const float3* __restrict__ wv, const float* __restrict__ normals,
             const uint32_t* __restrict__ order, const uint32_t* __restrict__ tri_mesh,
             const MeshInfo* __restrict__ meshes, const int32_t* __restrict__ indices,
             const float* __restrict__ texcoords, TriRecord* __restrict__ tris,
@@ -320,19 +313,24 @@ k_emit_tris(int n, const float3* __restrict__ wv, const float3* __restrict__ wn,
     const uint32_t g = order[s];
     const uint32_t m = tri_mesh[g];
     tris[s] = tri_pack(wv[3 * g], wv[3 * g + 1], wv[3 * g + 2], g, m);
-    const float3 n0 = wn[3 * g], n1 = wn[3 * g + 1], n2 = wn[3 * g + 2];
+    const MeshInfo& mi = meshes[m];
+    const int i0 = indices[3 * g] + mi.vtx_offset, i1 = indices[3 * g + 1] + mi.vtx_offset,
+              i2 = indices[3 * g + 2] + mi.vtx_offset;
+    float3 n0 = v3(0.0f), n1 = v3(0.0f), n2 = v3(0.0f);
+    if (mi.has_normals) {
+        n0 = v3(normals[3 * i0], normals[3 * i0 + 1], normals[3 * i0 + 2]);
+        n1 = v3(normals[3 * i1], normals[3 * i1 + 1], normals[3 * i1 + 2]);
+        n2 = v3(normals[3 * i2], normals[3 * i2 + 1], normals[3 * i2 + 2]);
+    }
     NrmRecord nr;
     nr.a = make_float4(n0.x, n0.y, n0.z, n1.x);
     nr.b = make_float4(n1.y, n1.z, n2.x, n2.y);
-    nr.c = make_float4(n2.z, __uint_as_float((uint32_t)meshes[m].has_normals), 0.0f, 0.0f);
+    nr.c = make_float4(n2.z, __uint_as_float((uint32_t)mi.has_normals), 0.0f, 0.0f);
     nrms[s] = nr;
     if (uvs) {
         UvRecord ur;
         ur.t0 = ur.t1 = ur.t2 = make_float2(0.0f, 0.0f);
-        const MeshInfo& mi = meshes[m];
         if (mi.has_uv) {
-            const int i0 = indices[3 * g] + mi.vtx_offset, i1 = indices[3 * g + 1] + mi.vtx_offset,
-                      i2 = indices[3 * g + 2] + mi.vtx_offset;
             ur.t0 = make_float2(texcoords[2 * i0], texcoords[2 * i0 + 1]);
             ur.t1 = make_float2(texcoords[2 * i1], texcoords[2 * i1 + 1]);
             ur.t2 = make_float2(texcoords[2 * i2], texcoords[2 * i2 + 1]);
@@ -460,7 +458,8 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
         mr.tex_albedo = tex_ok(me.tex_albedo);
         mr.tex_normal = tex_ok(me.tex_normal);
         mr.tex_metal_rough = tex_ok(me.tex_metal_rough);
-        if (mr.tex_albedo >= 0 && me.texcoords) any_alpha = 1;
+        memcpy(mr.mcol, me.model, sizeof mr.mcol);
+        if (mr.tex_albedo >= 0) any_alpha = 1;  // meshes without texcoords read uv = (0,0)
         vo += me.n_vertices;
         to += me.n_triangles;
     }
@@ -487,7 +486,7 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
     DeviceBuffer<int32_t> d_idx;
     DeviceBuffer<uint32_t> d_tri_mesh, d_vals[2], d_hist;
     DeviceBuffer<MeshInfo> d_infos;
-    DeviceBuffer<float3> d_wv, d_wn;
+    DeviceBuffer<float3> d_wv;
     DeviceBuffer<uint64_t> d_keys[2];
     DeviceBuffer<BoundsOrd> d_bounds;
     DeviceBuffer<int2> d_children;
@@ -500,7 +499,6 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
     d_tri_mesh.upload(tri_mesh.data(), tri_mesh.size(), stream);
     d_infos.upload(infos.data(), infos.size(), stream);
     d_wv.alloc((size_t)n * 3);
-    d_wn.alloc((size_t)n * 3);
     d_keys[0].alloc(n); d_keys[1].alloc(n);
     d_vals[0].alloc(n); d_vals[1].alloc(n);
     d_bounds.alloc(1);
@@ -518,8 +516,7 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
 
     k_init_bounds<<<1, 1, 0, stream>>>(d_bounds.get());
     k_flatten<<<blocks_for(n), kThreads, 0, stream>>>(n, d_idx.get(), d_tri_mesh.get(), d_infos.get(),
-                                                       d_pos.get(), d_nrm.get(), d_wv.get(), d_wn.get(),
-                                                       d_bounds.get());
+                                                       d_pos.get(), d_wv.get(), d_bounds.get());
     B2PT_CUDA(cudaGetLastError());
     BoundsOrd hb;
     d_bounds.download(&hb, 1, stream);
@@ -562,7 +559,7 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
     } else {
         k_emit_single<<<1, 1, 0, stream>>>(d_wv.get(), pad, out.nodes.get());
     }
-    k_emit_tris<<<blocks_for(n), kThreads, 0, stream>>>(n, d_wv.get(), d_wn.get(), order, d_tri_mesh.get(),
+    k_emit_tris<<<blocks_for(n), kThreads, 0, stream>>>(n, d_wv.get(), d_nrm.get(), order, d_tri_mesh.get(),
                                                          d_infos.get(), d_idx.get(), d_uv.get(),
                                                          out.tris.get(), out.nrms.get(), out.uvs.get());
     B2PT_CUDA(cudaGetLastError());

@@ -17,7 +17,10 @@
 namespace b2pt {
 
 // per-mesh material constants: MeshSBTData.albedoColor/roughness/metallic +
-// texture ids (Mesh.h:29-37).  32 bytes, two LDG.128.
+// texture ids (Mesh.h:29-37) + the first three columns of modelMatrix, which
+// GetNormal applies to the interpolated object-space normal
+// (devicePrograms.cu:96-100).  80 bytes, five LDG.128; the table has one entry
+// per mesh and stays cache-resident.
 struct alignas(16) MaterialRecord {
     float albedo[3];
     float metallic;
@@ -25,8 +28,9 @@ struct alignas(16) MaterialRecord {
     int32_t tex_albedo;   // < 0: none
     int32_t tex_normal;
     int32_t tex_metal_rough;
+    float mcol[12];       // modelMatrix columns 0..2, 4 rows each (column-major)
 };
-static_assert(sizeof(MaterialRecord) == 32, "material record must be 32 bytes");
+static_assert(sizeof(MaterialRecord) == 80, "material record must be 80 bytes");
 
 struct MeshInfo {
     float model[16];  // column-major

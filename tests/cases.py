@@ -66,3 +66,55 @@ def edge_rays():
     d = np.array(d, dtype=f32)
     d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(f32)
     return o, d
+
+
+# ---------------------------------------------------------------------------
+# BSDF rows: roughness x wo lattice (incl. grazing and back side)
+# x albedo set x LCG seeds.
+# ---------------------------------------------------------------------------
+ROUGHNESS = (0.0, 0.02, 0.1, 0.3, 0.5, 0.8, 1.0)
+ALBEDOS = ((0.8, 0.05, 0.05), (1.0, 1.0, 1.0), (0.2, 0.5, 0.9), (0.0, 0.3, 0.9999))
+
+
+def hemisphere_lattice(n_theta=7, n_phi=6, both_sides=True):
+    out = []
+    for it in range(n_theta):
+        ct = 1.0 - (it + 0.35) / n_theta * 0.999        # from ~1 down to grazing
+        st = np.sqrt(max(0.0, 1 - ct * ct))
+        for ip in range(n_phi):
+            ph = 2 * np.pi * (ip + 0.21 * it) / n_phi
+            out.append((st * np.cos(ph), st * np.sin(ph), ct))
+            if both_sides:
+                out.append((st * np.cos(ph + 0.3), st * np.sin(ph + 0.3), -ct))
+    out.append((0.0, 0.0, 1.0))
+    out.append((0.0, 0.0, -1.0))
+    d = np.array(out, dtype=np.float64)
+    return (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(f32)
+
+
+def bsdf_rows(seed=1, seeds_per_case=3, with_wi=True):
+    """Rows for the f / sample / pdf hooks: dict of flat arrays."""
+    rng = np.random.default_rng(seed)
+    wos = hemisphere_lattice()
+    rows = []
+    for r in ROUGHNESS:
+        for a in ALBEDOS:
+            for wo in wos:
+                for _ in range(seeds_per_case):
+                    rows.append((a, r, wo))
+    n = len(rows)
+    albedo = np.array([x[0] for x in rows], dtype=f32)
+    rough = np.array([x[1] for x in rows], dtype=f32)
+    wo = np.array([x[2] for x in rows], dtype=f32)
+    seeds = rng.integers(0, 2**32, n, dtype=np.uint64).astype(np.uint32)
+    out = {"albedo": albedo, "roughness": rough, "wo": wo, "seed": seeds}
+    if with_wi:
+        wi = rng.normal(size=(n, 3))
+        wi /= np.linalg.norm(wi, axis=1, keepdims=True)
+        # a third of the rows near the mirror direction (where rough lobes are non-trivial)
+        k = np.arange(n) % 3 == 0
+        mirror = wo * np.array([-1, -1, 1], dtype=f32)
+        wi[k] = mirror[k] + rng.normal(scale=0.15, size=(k.sum(), 3))
+        wi /= np.linalg.norm(wi, axis=1, keepdims=True)
+        out["wi"] = wi.astype(f32)
+    return out

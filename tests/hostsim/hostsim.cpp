@@ -179,3 +179,249 @@ void hostsim_trace_any(const float* org, const float* dir, int64_t n, float tmin
 }
 
 }  // extern "C"
+
+// ---- BSDF rows (bsdf_rows.cuh) on the host ---------------------------------
+#include "../../include/b2pt.h"
+#include "../../optixpathtracer_b200/csrc/bsdf_rows.cuh"
+
+extern "C" {
+
+void hostsim_bsdf_f(int bsdf, int lcg_mode, int64_t n, const float* albedo, const float* roughness,
+                    const float* wo, const float* wi, const uint32_t* seed, float* f_out, uint32_t* seed_out) {
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        if (lcg_mode == B2PT_RNG_LCG_HOST)
+            bsdf_row_f<LcgRng<true>>(bsdf, i, albedo, roughness, wo, wi, seed, f_out, seed_out);
+        else
+            bsdf_row_f<LcgRng<false>>(bsdf, i, albedo, roughness, wo, wi, seed, f_out, seed_out);
+    }
+}
+
+void hostsim_bsdf_sample(int bsdf, int lcg_mode, int64_t n, const float* albedo, const float* roughness,
+                         const float* wo, const uint32_t* seed, uint8_t* ok, float* f_out, float* wi_out,
+                         float* pdf_out, uint8_t* flags_out, uint32_t* seed_out) {
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; i++) {
+        if (lcg_mode == B2PT_RNG_LCG_HOST)
+            bsdf_row_sample<LcgRng<true>>(bsdf, i, albedo, roughness, wo, seed, ok, f_out, wi_out, pdf_out,
+                                          flags_out, seed_out);
+        else
+            bsdf_row_sample<LcgRng<false>>(bsdf, i, albedo, roughness, wo, seed, ok, f_out, wi_out, pdf_out,
+                                           flags_out, seed_out);
+    }
+}
+
+void hostsim_bsdf_pdf(int bsdf, int64_t n, const float* roughness, const float* wo, const float* wi,
+                      int reflection, int transmission, float* pdf_out) {
+    for (int64_t i = 0; i < n; i++)
+        bsdf_row_pdf(bsdf, i, roughness, wo, wi, reflection != 0, transmission != 0, pdf_out);
+}
+
+}  // extern "C"
+
+// ---- whole frames: the wavefront stages (integrator.cuh) run per pixel --------
+#include "../../optixpathtracer_b200/csrc/integrator.cuh"
+
+namespace {
+
+struct HostTexFetch {   // same filter as oracle/ref_harness.cpp::shim_tex2d
+    const B2ptTexture* tex;
+    static float4 texel(const B2ptTexture& t, int x, int y) {
+        x = ((x % t.width) + t.width) % t.width;
+        y = ((y % t.height) + t.height) % t.height;
+        const uint8_t* p = t.rgba + 4 * ((size_t)y * t.width + x);
+        return make_float4(p[0] / 255.0f, p[1] / 255.0f, p[2] / 255.0f, p[3] / 255.0f);
+    }
+    float4 operator()(int id, float x, float y) const {
+        const B2ptTexture& t = tex[id];
+        const float xb = x * (float)t.width - 0.5f, yb = y * (float)t.height - 0.5f;
+        const float fx = floorf(xb), fy = floorf(yb);
+        const float a = floorf((xb - fx) * 256.0f + 0.5f) / 256.0f, b = floorf((yb - fy) * 256.0f + 0.5f) / 256.0f;
+        const int i = (int)fx, j = (int)fy;
+        const float4 t00 = texel(t, i, j), t10 = texel(t, i + 1, j), t01 = texel(t, i, j + 1), t11 = texel(t, i + 1, j + 1);
+        auto mixc = [&](float c00, float c10, float c01, float c11) {
+            return (1 - a) * (1 - b) * c00 + a * (1 - b) * c10 + (1 - a) * b * c01 + a * b * c11;
+        };
+        return make_float4(mixc(t00.x, t10.x, t01.x, t11.x), mixc(t00.y, t10.y, t01.y, t11.y),
+                           mixc(t00.z, t10.z, t01.z, t11.z), mixc(t00.w, t10.w, t01.w, t11.w));
+    }
+};
+
+struct HostScene {
+    HostBvh bvh;
+    std::vector<NrmRecord> nrms;
+    std::vector<UvRecord> uvs;
+    std::vector<MaterialRecord> mats;
+    std::vector<std::vector<uint8_t>> tex_pixels;
+    std::vector<B2ptTexture> textures;
+    DeviceScene view;
+};
+
+template <class Rng>
+float3 trace_path(const HostScene& hs, const CameraParams& cam, int x, int y, uint32_t frame_id, uint64_t seed,
+                  const B2ptPointLight* lights, int n_lights, int max_bounces, int mode, uint64_t* rays) {
+    PathVertex pv;
+    pv.beta = v3(1.0f);
+    pv.radiance = v3(0.0f);
+    camera_ray(cam, x, y, pv.next_o, pv.next_d);
+    RngCtx ctx;
+    ctx.seed = seed;
+    ctx.pixel = (uint32_t)(cam.width * y + x);
+    ctx.sample = frame_id;
+    ctx.lcg_state = RngIO<Rng>::first_state(ctx.pixel, frame_id);
+    const HostTexFetch tex{hs.textures.data()};
+    for (int bounce = 0; path_continues(pv.beta, bounce, max_bounces); bounce++) {
+        ctx.bounce = (uint32_t)bounce;
+        HitRecord hit;
+        rays[0]++;
+        if (!traverse<false, false>(hs.view.nodes, hs.view.tris, hs.view.n_nodes, pv.next_o, pv.next_d, 0.0f, 100.0f,
+                                    hit, nullptr))
+            break;   // __miss__radiance
+        const float3 ray_d = pv.next_d;
+        SurfacePoint sp;
+        {
+            Rng rng = RngIO<Rng>::open(ctx, 0);
+            surface_stage(hs.view, tex, hit, ray_d, lights, n_lights, rng, sp);
+            ctx.lcg_state = RngIO<Rng>::close(rng);
+        }
+        bool visible = false;
+        if (sp.light >= 0) {
+            HitRecord sh;
+            rays[1]++;
+            visible = !traverse<true, false>(hs.view.nodes, hs.view.tris, hs.view.n_nodes, sp.sh_o, sp.sh_d, 0.0f,
+                                             sp.sh_tmax, sh, nullptr);
+        }
+        int kind = mode - 1;
+        if (mode == B2PT_BSDF_AUTO) kind = sp.conductor ? kBsdfConductor : kBsdfLayered;
+        Rng rng = RngIO<Rng>::open(ctx, 1);
+        bool alive = false;
+        switch (kind) {
+            case kBsdfConductor: alive = shade_stage<kBsdfConductor>(sp, visible, ray_d, lights, n_lights, rng, pv); break;
+            case kBsdfDiffuse: alive = shade_stage<kBsdfDiffuse>(sp, visible, ray_d, lights, n_lights, rng, pv); break;
+            case kBsdfDielectric: alive = shade_stage<kBsdfDielectric>(sp, visible, ray_d, lights, n_lights, rng, pv); break;
+            default: alive = shade_stage<kBsdfLayered>(sp, visible, ray_d, lights, n_lights, rng, pv); break;
+        }
+        ctx.lcg_state = RngIO<Rng>::close(rng);
+        if (!alive) break;
+    }
+    return pv.radiance;
+}
+
+}  // namespace
+
+extern "C" {
+
+void* hostsim_scene_create(const B2ptSceneDesc* desc) {
+    HostScene* hs = new HostScene();
+    std::vector<float> soup;
+    std::vector<uint32_t> tri_mesh;
+    std::vector<int32_t> tri_local;
+    bool any_uv = false;
+    for (int m = 0; m < desc->n_meshes; m++) {
+        const B2ptMesh& me = desc->meshes[m];
+        any_uv |= me.texcoords != nullptr;
+        for (int t = 0; t < me.n_triangles; t++) {
+            for (int k = 0; k < 3; k++) {
+                const float* p = me.positions + 3 * me.indices[3 * t + k];
+                const float4 w = mat4_mul(me.model, p[0], p[1], p[2], 1.0f);   // k_flatten
+                soup.push_back(w.x); soup.push_back(w.y); soup.push_back(w.z);
+            }
+            tri_mesh.push_back((uint32_t)m);
+            tri_local.push_back(t);
+        }
+        MaterialRecord mr;
+        memcpy(mr.albedo, me.albedo, 12);
+        mr.metallic = me.metallic;
+        mr.roughness = me.roughness;
+        auto ok = [&](int t) { return (t >= 0 && t < desc->n_textures) ? t : -1; };
+        mr.tex_albedo = ok(me.tex_albedo);
+        mr.tex_normal = ok(me.tex_normal);
+        mr.tex_metal_rough = ok(me.tex_metal_rough);
+        memcpy(mr.mcol, me.model, sizeof mr.mcol);
+        hs->mats.push_back(mr);
+    }
+    const int n = (int)tri_mesh.size();
+    build(soup.data(), n, hs->bvh);
+    hs->nrms.resize(n);
+    if (any_uv) hs->uvs.resize(n);
+    for (int s = 0; s < n; s++) {
+        const uint32_t g = hs->bvh.order[s];
+        const B2ptMesh& me = desc->meshes[tri_mesh[g]];
+        hs->bvh.tris[s].c.z = u2f_bits(tri_mesh[g]);   // mesh id next to the primitive id
+        const int32_t* ix = me.indices + 3 * tri_local[g];
+        float nn[9] = {0};
+        if (me.normals)
+            for (int k = 0; k < 3; k++) memcpy(nn + 3 * k, me.normals + 3 * ix[k], 12);
+        NrmRecord nr;
+        nr.a = make_float4(nn[0], nn[1], nn[2], nn[3]);
+        nr.b = make_float4(nn[4], nn[5], nn[6], nn[7]);
+        nr.c = make_float4(nn[8], u2f_bits(me.normals ? 1u : 0u), 0.0f, 0.0f);
+        hs->nrms[s] = nr;
+        if (any_uv) {
+            UvRecord ur;
+            ur.t0 = ur.t1 = ur.t2 = make_float2(0.0f, 0.0f);
+            if (me.texcoords) {
+                ur.t0 = make_float2(me.texcoords[2 * ix[0]], me.texcoords[2 * ix[0] + 1]);
+                ur.t1 = make_float2(me.texcoords[2 * ix[1]], me.texcoords[2 * ix[1] + 1]);
+                ur.t2 = make_float2(me.texcoords[2 * ix[2]], me.texcoords[2 * ix[2] + 1]);
+            }
+            hs->uvs[s] = ur;
+        }
+    }
+    for (int i = 0; i < desc->n_textures; i++) {
+        const B2ptTexture& t = desc->textures[i];
+        hs->tex_pixels.emplace_back(t.rgba, t.rgba + (size_t)t.width * t.height * 4);
+        hs->textures.push_back(B2ptTexture{hs->tex_pixels.back().data(), t.width, t.height});
+    }
+    DeviceScene& v = hs->view;
+    memset(&v, 0, sizeof v);
+    v.nodes = hs->bvh.nodes.data();
+    v.tris = hs->bvh.tris.data();
+    v.nrms = hs->nrms.data();
+    v.uvs = any_uv ? hs->uvs.data() : nullptr;
+    v.materials = hs->mats.data();
+    v.n_nodes = (int)hs->bvh.nodes.size();
+    v.n_tris = n;
+    v.n_meshes = desc->n_meshes;
+    v.n_textures = desc->n_textures;
+    return hs;
+}
+
+void hostsim_scene_destroy(void* h) { delete static_cast<HostScene*>(h); }
+
+// frames_out: n_frames * H * W * 3; rays: [radiance, shadow]
+void hostsim_render(void* h, int width, int height, const float* cam_pos, const float* inv_view,
+                    const float* inv_proj, const B2ptPointLight* lights, int n_lights, int max_bounces, int mode,
+                    int rng_mode, uint64_t seed, uint32_t frame_first, int n_frames, float* frames_out,
+                    uint64_t* rays_out) {
+    const HostScene& hs = *static_cast<HostScene*>(h);
+    CameraParams cam;
+    cam.position = v3(cam_pos[0], cam_pos[1], cam_pos[2]);
+    memcpy(cam.inv_view, inv_view, 64);
+    memcpy(cam.inv_proj, inv_proj, 64);
+    cam.width = width;
+    cam.height = height;
+    uint64_t r0 = 0, r1 = 0;
+    for (int f = 0; f < n_frames; f++) {
+        const uint32_t fid = frame_first + (uint32_t)f;
+#pragma omp parallel for schedule(dynamic, 1) reduction(+ : r0, r1)
+        for (int y = 0; y < height; y++)
+            for (int x = 0; x < width; x++) {
+                uint64_t rays[2] = {0, 0};
+                float3 c;
+                if (rng_mode == B2PT_RNG_LCG_HOST)
+                    c = trace_path<LcgRng<true>>(hs, cam, x, y, fid, seed, lights, n_lights, max_bounces, mode, rays);
+                else if (rng_mode == B2PT_RNG_LCG_DEVICE)
+                    c = trace_path<LcgRng<false>>(hs, cam, x, y, fid, seed, lights, n_lights, max_bounces, mode, rays);
+                else
+                    c = trace_path<PhiloxRng>(hs, cam, x, y, fid, seed, lights, n_lights, max_bounces, mode, rays);
+                float* o = frames_out + ((size_t)f * width * height + (size_t)y * width + x) * 3;
+                o[0] = c.x; o[1] = c.y; o[2] = c.z;
+                r0 += rays[0];
+                r1 += rays[1];
+            }
+    }
+    if (rays_out) { rays_out[0] = r0; rays_out[1] = r1; }
+}
+
+}  // extern "C"

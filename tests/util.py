@@ -109,6 +109,70 @@ class HostSim:
                                        vp(prim), fp(t), fp(u), fp(v), vp(bf), cnt)
         return prim, t, u, v, bf, tuple(cnt)
 
+    def render(self, scene, width, height, *, bsdf_mode=0, rng_mode=2, seed=0x5EED, max_bounces=8,
+               frame_first=1, n_frames=1, lights=None):
+        """The wavefront stages (integrator.cuh) run per pixel on the host.
+        Returns (frames (n,H,W,3), {"radiance_rays", "shadow_rays"})."""
+        from optixpathtracer_b200.api import _SceneMarshal
+        from optixpathtracer_b200._lib import B2ptPointLight
+        self.lib.hostsim_scene_create.restype = C.c_void_p
+        m = _SceneMarshal(scene)
+        h = C.c_void_p(self.lib.hostsim_scene_create(C.byref(m.desc)))
+        try:
+            pos, iv, ip = scene["camera"].launch_matrices(width, height)
+            lights = scene["lights"] if lights is None else lights
+            arr = (B2ptPointLight * max(len(lights), 1))()
+            for i, (p, c) in enumerate(lights):
+                arr[i].position = (C.c_float * 3)(*np.asarray(p, dtype=f32))
+                arr[i].color = (C.c_float * 3)(*np.asarray(c, dtype=f32))
+            frames = np.empty((n_frames, height, width, 3), f32)
+            rays = (C.c_uint64 * 2)()
+            self.lib.hostsim_render(h, C.c_int(width), C.c_int(height), fp(pos), fp(iv), fp(ip), arr,
+                                    C.c_int(len(lights)), C.c_int(max_bounces), C.c_int(bsdf_mode),
+                                    C.c_int(rng_mode), C.c_uint64(seed), C.c_uint32(frame_first),
+                                    C.c_int(n_frames), fp(frames), rays)
+        finally:
+            self.lib.hostsim_scene_destroy(h)
+        return frames, {"radiance_rays": rays[0], "shadow_rays": rays[1]}
+
+    # BSDF rows: same signatures as RefOracle.bsdf_* plus the LCG flavour
+    def bsdf_f(self, bsdf, albedo, roughness, wo, wi, seed=None, lcg_mode=2):
+        wo = np.ascontiguousarray(wo, dtype=f32).reshape(-1, 3)
+        wi = np.ascontiguousarray(wi, dtype=f32).reshape(-1, 3)
+        n = len(wo)
+        a, r = RefOracle._prep(n, albedo, roughness)
+        sd = np.ascontiguousarray(np.broadcast_to(np.asarray(0 if seed is None else seed, dtype=np.uint32), (n,)), dtype=np.uint32)
+        out = np.empty((n, 3), f32)
+        so = np.empty(n, np.uint32)
+        self.lib.hostsim_bsdf_f(C.c_int(bsdf), C.c_int(lcg_mode), C.c_int64(n), fp(a), fp(r), fp(wo), fp(wi),
+                                vp(sd), fp(out), vp(so))
+        return out, so
+
+    def bsdf_sample(self, bsdf, albedo, roughness, wo, seed, lcg_mode=2):
+        wo = np.ascontiguousarray(wo, dtype=f32).reshape(-1, 3)
+        n = len(wo)
+        a, r = RefOracle._prep(n, albedo, roughness)
+        sd = np.ascontiguousarray(np.broadcast_to(np.asarray(seed, dtype=np.uint32), (n,)), dtype=np.uint32)
+        ok = np.empty(n, np.uint8)
+        f = np.empty((n, 3), f32)
+        wi = np.empty((n, 3), f32)
+        pdf = np.empty(n, f32)
+        flags = np.empty(n, np.uint8)
+        so = np.empty(n, np.uint32)
+        self.lib.hostsim_bsdf_sample(C.c_int(bsdf), C.c_int(lcg_mode), C.c_int64(n), fp(a), fp(r), fp(wo), vp(sd),
+                                     vp(ok), fp(f), fp(wi), fp(pdf), vp(flags), vp(so))
+        return ok, f, wi, pdf, flags, so
+
+    def bsdf_pdf(self, bsdf, roughness, wo, wi, reflection=True, transmission=True):
+        wo = np.ascontiguousarray(wo, dtype=f32).reshape(-1, 3)
+        wi = np.ascontiguousarray(wi, dtype=f32).reshape(-1, 3)
+        n = len(wo)
+        _, r = RefOracle._prep(n, (1, 1, 1), roughness)
+        out = np.empty(n, f32)
+        self.lib.hostsim_bsdf_pdf(C.c_int(bsdf), C.c_int64(n), fp(r), fp(wo), fp(wi), C.c_int(int(reflection)),
+                                  C.c_int(int(transmission)), fp(out))
+        return out
+
     def any(self, org, dirs, tmax, tmin=0.0):
         o = np.ascontiguousarray(org, dtype=f32).reshape(-1, 3)
         d = np.ascontiguousarray(dirs, dtype=f32).reshape(-1, 3)
