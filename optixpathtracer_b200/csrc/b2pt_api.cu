@@ -273,8 +273,8 @@ int b2pt_get_stats(const B2ptRenderer* rc, B2ptStats* out) {
         B2PT_CUDA(cudaMemcpy(&c, r->d_counters.get(), sizeof c, cudaMemcpyDeviceToHost));
         memset(out, 0, sizeof *out);
         out->samples = r->samples;
-        out->radiance_rays = c.radiance_rays;
-        out->shadow_rays = c.shadow_rays;
+        out->radiance_rays = c.radiance_rays + r->hook_radiance_rays;
+        out->shadow_rays = c.shadow_rays + r->hook_shadow_rays;
         out->nodes_visited = c.nodes;
         out->triangles_tested = c.tris;
         out->exact_tests = c.exact;
@@ -296,6 +296,7 @@ int b2pt_reset_stats(B2ptRenderer* r) {
         r->d_counters.zero(r->stream);
         r->samples = 0;
         r->kernel_launches = 0;
+        r->hook_radiance_rays = r->hook_shadow_rays = 0;
         r->device_ms_render = 0.0;
         B2PT_CUDA(cudaStreamSynchronize(r->stream));
     });
@@ -324,6 +325,7 @@ int b2pt_trace_closest(B2ptRenderer* r, int64_t n, const float* org, const float
         st.ox = d_o.get(); st.oy = d_o.get() + n; st.oz = d_o.get() + 2 * n;
         st.dx = d_d.get(); st.dy = d_d.get() + n; st.dz = d_d.get() + 2 * n;
         launch_closest(launch_cfg(r), r->scene.view(), st, d_n.get(), tmin, tmax, d_h.get(), r->d_counters.get());
+        r->hook_radiance_rays += (uint64_t)n;
         B2PT_CUDA(cudaGetLastError());
         std::vector<HitRecord> hh((size_t)n);
         d_h.download(hh.data(), hh.size(), r->stream);
@@ -372,6 +374,7 @@ int b2pt_trace_any(B2ptRenderer* r, int64_t n, const float* org, const float* di
         sh.dx = d_d.get(); sh.dy = d_d.get() + n; sh.dz = d_d.get() + 2 * n;
         sh.tmax = d_t.get();
         launch_any(launch_cfg(r), r->scene.view(), sh, d_n.get(), tmin, nullptr, d_occ.get(), r->d_counters.get());
+        r->hook_shadow_rays += (uint64_t)n;
         B2PT_CUDA(cudaGetLastError());
         d_occ.download(occluded, (size_t)n, r->stream);
         B2PT_CUDA(cudaStreamSynchronize(r->stream));

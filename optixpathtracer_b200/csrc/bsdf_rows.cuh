@@ -3,6 +3,7 @@
 // B2PT_HD so that the CPU test tier (tests/hostsim) can run the identical code.
 #pragma once
 
+#include "../../include/b2pt.h"
 #include "bsdf.cuh"
 
 namespace b2pt {

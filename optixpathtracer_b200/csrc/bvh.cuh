@@ -18,6 +18,13 @@
 
 #include "vecmath.cuh"
 
+// 128-bit read-only loads of the 16-byte-aligned records below
+#if defined(__CUDA_ARCH__)
+#define B2PT_LDG4(p) __ldg(reinterpret_cast<const float4*>(p))
+#else
+#define B2PT_LDG4(p) (*reinterpret_cast<const float4*>(p))
+#endif
+
 namespace b2pt {
 
 struct alignas(16) BvhNode2 {

@@ -51,6 +51,7 @@ struct B2ptRenderer {
     // statistics
     uint64_t samples = 0;
     uint64_t kernel_launches = 0;
+    uint64_t hook_radiance_rays = 0, hook_shadow_rays = 0;   // rays traced by the parity hooks
     double device_ms_render = 0.0;
 
     void set_error(const std::string& m) { last_error = m; }

@@ -129,18 +129,20 @@ B2PT_HD bool slab(const RaySetup& r, float lox, float hix, float loy, float hiy,
 constexpr int kStackSize = 64;
 constexpr int kStackSentinel = 0x7fffffff;
 
-#if defined(__CUDA_ARCH__)
-#define B2PT_LDG4(p) __ldg(reinterpret_cast<const float4*>(p))
-#else
-#define B2PT_LDG4(p) (*reinterpret_cast<const float4*>(p))
-#endif
+
+// The any-hit program as a predicate on a candidate hit (A9): the default
+// accepts everything and compiles to nothing; scenes with albedo textures use
+// AlphaCutout (alpha.cuh).
+struct AcceptAllHits {
+    B2PT_HD bool operator()(uint32_t /*slot*/, uint32_t /*mesh*/, float /*u*/, float /*v*/) const { return true; }
+};
 
 // ANY = false: closest hit into `hit`; returns hit != miss.
 // ANY = true : returns true as soon as one triangle is hit in (tmin, tmax).
-template <bool ANY, bool STATS>
+template <bool ANY, bool STATS, class Accept = AcceptAllHits>
 B2PT_HD bool traverse(const BvhNode2* __restrict__ nodes, const TriRecord* __restrict__ tris,
                       int n_nodes, float3 o, float3 d, float tmin, float tmax, HitRecord& hit,
-                      TraceStats* stats) {
+                      TraceStats* stats, const Accept& accept = Accept()) {
     hit.tri = kHitMiss;
     hit.t = hit.u = hit.v = 0.0f;
     if (n_nodes <= 0) return false;
@@ -191,11 +193,16 @@ B2PT_HD bool traverse(const BvhNode2* __restrict__ nodes, const TriRecord* __res
                 bool bf;
                 if (tri_exact(r.o, r.d, v0, v1, v2, t, u, v, bf) && t > tmin_d && t < tmax_d) {
                     if (ANY) {
-                        hit.tri = (uint32_t)slot;
-                        return true;
+                        if (accept((uint32_t)slot, f2u_bits(tc.z), (float)u, (float)v)) {
+                            hit.tri = (uint32_t)slot;
+                            return true;
+                        }
+                        node = stack[--sp];
+                        continue;
                     }
                     const uint32_t prim = f2u_bits(tc.y);
-                    if (t < best_t || (t == best_t && prim < best_prim)) {
+                    if ((t < best_t || (t == best_t && prim < best_prim)) &&
+                        accept((uint32_t)slot, f2u_bits(tc.z), (float)u, (float)v)) {
                         best_t = t;
                         best_prim = prim;
                         // round up so the fp32 culling bound never cuts below best_t

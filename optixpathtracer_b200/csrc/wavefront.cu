@@ -1,11 +1,407 @@
-// wavefront.cu — placeholder for slice 1 (replaced by the integrator).
+// wavefront.cu — the wavefront integrator: kernels K4, K6, K7a-d, K9 and the
+// host-side scheduler that replaces the reference's megakernel launch
+// (OptixRenderer::Render, OptixRenderer.cpp:617-647 -> optixLaunch(W, H, 1) of
+// __raygen__renderFrame, devicePrograms.cu:667-706).
+//
+// One WAVE = a tile of `np` pixels x `spw` consecutive samples, all paths in
+// flight at once in structure-of-arrays buffers.  Per bounce b:
+//
+//   K5 k_closest   rays of st[b&1][0 .. n_b)            -> hits          (trace_kernels.cu)
+//   K6 k_surface   hit -> surface record, class draw, light pick, shadow ray;
+//                  misses retire; hits are appended to the queue of their BSDF
+//   K8 k_any       shadow rays -> visible bit                            (trace_kernels.cu)
+//   K7 k_shade<B>  one launch per BSDF present: NEE add, BSDF sample, throughput,
+//                  next ray; survivors are compacted into st[(b+1)&1]
+//
+// and once per wave K4 k_raygen before, K9 k_accumulate after.  All counts
+// (n_b, queue lengths) live in device memory; the host enqueues the whole wave
+// without ever synchronising.
+//
+// Determinism: a path's arithmetic depends only on (pixel, sample index, seed);
+// where a path sits in the buffers (atomics order) never enters the result, and
+// K9 adds the samples of a pixel in sample order.  Same inputs => same bits.
+#include <algorithm>
+#include <cstring>
+
 #include "render.h"
+#include "integrator.cuh"
+
 namespace b2pt {
-void render_frames(B2ptRenderer*, int, bool) { throw Error{B2PT_E_UNSUPPORTED, "integrator not built in this slice"}; }
-void resolve_mean(B2ptRenderer*) {}
-}  // namespace b2pt
-extern "C" {
-int b2pt_bsdf_f(int32_t, int32_t, int32_t, int64_t, const float*, const float*, const float*, const float*, const uint32_t*, float*, uint32_t*) { return B2PT_E_UNSUPPORTED; }
-int b2pt_bsdf_sample(int32_t, int32_t, int32_t, int64_t, const float*, const float*, const float*, const uint32_t*, uint8_t*, float*, float*, float*, uint8_t*, uint32_t*) { return B2PT_E_UNSUPPORTED; }
-int b2pt_bsdf_pdf(int32_t, int32_t, int64_t, const float*, const float*, const float*, int32_t, int32_t, float*) { return B2PT_E_UNSUPPORTED; }
+
+namespace {
+
+constexpr int kThreads = 128;
+
+struct WaveParams {
+    CameraParams cam;
+    const B2ptPointLight* lights;
+    int32_t n_lights;
+    int32_t max_bounces;
+    int32_t mode;          // B2PT_BSDF_*
+    uint64_t seed;
+    uint32_t p0, np;       // pixel tile [p0, p0 + np)
+    uint32_t spw;          // samples in this wave
+    uint32_t frame0;       // frame.id of the wave's first sample
+    uint32_t capacity;     // slots per SoA array
+};
+
+// counters of one wave, zeroed before K4:  active[b] = rays traced at bounce b,
+// queued[b][k] = hits shaded with BSDF k at bounce b
+struct WaveCounts {
+    uint32_t* active;   // [max_bounces + 1]
+    uint32_t* queued;   // [max_bounces][4]
+};
+
+__device__ __forceinline__ void path_identity(const WaveParams& wp, uint32_t id, uint32_t& pixel, uint32_t& sample) {
+    const uint32_t s_local = id / wp.np;
+    pixel = wp.p0 + (id - s_local * wp.np);
+    sample = wp.frame0 + s_local;
 }
+
+// ---- K4 ----------------------------------------------------------------------
+template <class Rng>
+__global__ void __launch_bounds__(kThreads)
+k_raygen(WaveParams wp, PathState st, uint32_t* __restrict__ active0) {
+    const uint32_t n = wp.np * wp.spw;
+    if (blockIdx.x == 0 && threadIdx.x == 0) *active0 = n;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        uint32_t pixel, sample;
+        path_identity(wp, i, pixel, sample);
+        const int y = (int)(pixel / (uint32_t)wp.cam.width), x = (int)(pixel - (uint32_t)y * wp.cam.width);
+        float3 o, d;
+        camera_ray(wp.cam, x, y, o, d);
+        st.ox[i] = o.x; st.oy[i] = o.y; st.oz[i] = o.z;
+        st.dx[i] = d.x; st.dy[i] = d.y; st.dz[i] = d.z;
+        st.bx[i] = 1.0f; st.by[i] = 1.0f; st.bz[i] = 1.0f;
+        st.rx[i] = 0.0f; st.ry[i] = 0.0f; st.rz[i] = 0.0f;
+        st.id[i] = i;
+        st.seed[i] = RngIO<Rng>::first_state(pixel, sample);
+    }
+}
+
+// warp-aggregated append: every lane of the warp must call this
+__device__ __forceinline__ uint32_t warp_append(bool want, uint32_t* counter) {
+    const uint32_t mask = __ballot_sync(0xffffffffu, want);
+    if (mask == 0u) return 0u;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + (uint32_t)__popc(mask & ((1u << lane) - 1u));
+}
+
+// ---- K6 ----------------------------------------------------------------------
+template <class Rng>
+__global__ void __launch_bounds__(kThreads)
+k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restrict__ hits, SurfaceState sf,
+          ShadowRays sh, uint32_t* __restrict__ queues, WaveCounts wc, uint32_t bounce, float* __restrict__ wave_out) {
+    const uint32_t n = wc.active[bounce];
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t iters = (n + stride - 1) / stride;
+    const DeviceTexFetch tex{sc.textures};
+    uint32_t* qn = wc.queued + 4 * bounce;
+    for (uint32_t it = 0; it < iters; it++) {
+        const uint32_t i = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        int kind = -1;
+        if (i < n) {
+            const float4 hv = reinterpret_cast<const float4*>(hits)[i];
+            HitRecord hit;
+            hit.tri = __float_as_uint(hv.x); hit.t = hv.y; hit.u = hv.z; hit.v = hv.w;
+            if (hit.tri == kHitMiss) {   // __miss__radiance (:576-583): the path ends with what it has
+                const uint32_t id = st.id[i];
+                wave_out[id] = st.rx[i];
+                wave_out[wp.capacity + id] = st.ry[i];
+                wave_out[2 * wp.capacity + id] = st.rz[i];
+                sh.tmax[i] = -1.0f;
+            } else {
+                RngCtx ctx;
+                ctx.seed = wp.seed;
+                path_identity(wp, st.id[i], ctx.pixel, ctx.sample);
+                ctx.bounce = bounce;
+                ctx.lcg_state = st.seed[i];
+                Rng rng = RngIO<Rng>::open(ctx, 0);
+                SurfacePoint s;
+                surface_stage(sc, tex, hit, v3(st.dx[i], st.dy[i], st.dz[i]), wp.lights, wp.n_lights, rng, s);
+                st.seed[i] = RngIO<Rng>::close(rng);
+                sf.px[i] = s.p.x; sf.py[i] = s.p.y; sf.pz[i] = s.p.z;
+                sf.gx[i] = s.ng.x; sf.gy[i] = s.ng.y; sf.gz[i] = s.ng.z;
+                sf.nx[i] = s.ns.x; sf.ny[i] = s.ns.y; sf.nz[i] = s.ns.z;
+                sf.ar[i] = s.sp.albedo.x; sf.ag[i] = s.sp.albedo.y; sf.ab[i] = s.sp.albedo.z;
+                sf.rough[i] = s.sp.roughness;
+                sf.info[i] = (s.light >= 0 ? ((uint32_t)s.light | kInfoHasLight) : 0u) |
+                             (s.conductor ? kInfoConductor : 0u);
+                sh.ox[i] = s.sh_o.x; sh.oy[i] = s.sh_o.y; sh.oz[i] = s.sh_o.z;
+                sh.dx[i] = s.sh_d.x; sh.dy[i] = s.sh_d.y; sh.dz[i] = s.sh_d.z;
+                sh.tmax[i] = s.sh_tmax;
+                kind = wp.mode == B2PT_BSDF_AUTO ? (s.conductor ? kBsdfConductor : kBsdfLayered) : wp.mode - 1;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t pos = warp_append(kind == k, qn + k);
+            if (kind == k) queues[(size_t)k * wp.capacity + pos] = i;
+        }
+    }
+}
+
+// ---- K7a-d -------------------------------------------------------------------
+// One launch per BSDF: every thread of the kernel runs the same BSDF code.
+template <int KIND, class Rng>
+__global__ void __launch_bounds__(kThreads)
+k_shade(WaveParams wp, PathState st, PathState nx, SurfaceState sf, const uint32_t* __restrict__ queue,
+        WaveCounts wc, uint32_t bounce, float* __restrict__ wave_out) {
+    const uint32_t n = wc.queued[4 * bounce + KIND];
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t iters = (n + stride - 1) / stride;
+    for (uint32_t it = 0; it < iters; it++) {
+        const uint32_t q = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        bool alive = false;
+        PathVertex pv;
+        uint32_t id = 0, seed = 0;
+        if (q < n) {
+            const uint32_t i = queue[q];
+            SurfacePoint s;
+            s.p = v3(sf.px[i], sf.py[i], sf.pz[i]);
+            s.ng = v3(sf.gx[i], sf.gy[i], sf.gz[i]);
+            s.ns = v3(sf.nx[i], sf.ny[i], sf.nz[i]);
+            s.sp.albedo = v3(sf.ar[i], sf.ag[i], sf.ab[i]);
+            s.sp.roughness = sf.rough[i];
+            const uint32_t info = sf.info[i];
+            s.light = (info & kInfoHasLight) ? (int)(info & 0xffu) : -1;
+            s.conductor = (info & kInfoConductor) != 0;
+            pv.beta = v3(st.bx[i], st.by[i], st.bz[i]);
+            pv.radiance = v3(st.rx[i], st.ry[i], st.rz[i]);
+            pv.next_o = pv.next_d = v3(0.0f);
+            id = st.id[i];
+            RngCtx ctx;
+            ctx.seed = wp.seed;
+            path_identity(wp, id, ctx.pixel, ctx.sample);
+            ctx.bounce = bounce;
+            ctx.lcg_state = st.seed[i];
+            Rng rng = RngIO<Rng>::open(ctx, 1);
+            alive = shade_stage<KIND>(s, (info & kInfoVisible) != 0, v3(st.dx[i], st.dy[i], st.dz[i]), wp.lights,
+                                      wp.n_lights, rng, pv);
+            seed = RngIO<Rng>::close(rng);
+            alive = alive && path_continues(pv.beta, (int)bounce + 1, wp.max_bounces);
+            if (!alive) {   // radiance is final (:658)
+                wave_out[id] = pv.radiance.x;
+                wave_out[wp.capacity + id] = pv.radiance.y;
+                wave_out[2 * wp.capacity + id] = pv.radiance.z;
+            }
+        }
+        const uint32_t j = warp_append(alive, wc.active + bounce + 1);
+        if (alive) {
+            nx.ox[j] = pv.next_o.x; nx.oy[j] = pv.next_o.y; nx.oz[j] = pv.next_o.z;
+            nx.dx[j] = pv.next_d.x; nx.dy[j] = pv.next_d.y; nx.dz[j] = pv.next_d.z;
+            nx.bx[j] = pv.beta.x; nx.by[j] = pv.beta.y; nx.bz[j] = pv.beta.z;
+            nx.rx[j] = pv.radiance.x; nx.ry[j] = pv.radiance.y; nx.rz[j] = pv.radiance.z;
+            nx.id[j] = id;
+            nx.seed[j] = seed;
+        }
+    }
+}
+
+// ---- K9 ----------------------------------------------------------------------
+// Replaces the GL accumulate pass (AddPathtracedFrame.frag:13-25 driven by
+// OptixView.cpp:212-255): the samples of a pixel are added in sample order to
+// the fp32 sum (accumulate) or the single sample overwrites the frame (Render,
+// devicePrograms.cu:704-705).  Non-finite samples are zeroed and counted when
+// accumulating (the reference only repairs them when writing the EXR,
+// WriteImage.cpp:52-55); Render passes them through untouched.
+__global__ void __launch_bounds__(256)
+k_accumulate(WaveParams wp, const float* __restrict__ wave_out, float* __restrict__ dst, int overwrite,
+             TraceCounters* counters) {
+    uint32_t bad = 0;
+    for (uint32_t p = blockIdx.x * blockDim.x + threadIdx.x; p < wp.np; p += gridDim.x * blockDim.x) {
+        float* o = dst + 3 * (size_t)(wp.p0 + p);
+        if (overwrite) {
+            o[0] = wave_out[p];
+            o[1] = wave_out[wp.capacity + p];
+            o[2] = wave_out[2 * wp.capacity + p];
+            continue;
+        }
+        float r = o[0], g = o[1], b = o[2];
+        for (uint32_t s = 0; s < wp.spw; s++) {
+            const uint32_t id = s * wp.np + p;
+            const float sr = wave_out[id], sg = wave_out[wp.capacity + id], sb = wave_out[2 * wp.capacity + id];
+            if (isfinite(sr) && isfinite(sg) && isfinite(sb)) {
+                r += sr; g += sg; b += sb;
+            } else {
+                bad++;
+            }
+        }
+        o[0] = r; o[1] = g; o[2] = b;
+    }
+    if (bad) atomicAdd(&counters->nan_samples, (unsigned long long)bad);
+}
+
+// ray census of a finished wave (device-side, no host round trip)
+__global__ void k_tally(WaveCounts wc, int max_bounces, int has_lights, TraceCounters* counters) {
+    unsigned long long rr = 0, sr = 0;
+    for (int b = threadIdx.x; b < max_bounces; b += blockDim.x) {
+        rr += wc.active[b];
+        if (has_lights) sr += (unsigned long long)wc.queued[4 * b] + wc.queued[4 * b + 1] + wc.queued[4 * b + 2] + wc.queued[4 * b + 3];
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        rr += __shfl_xor_sync(0xffffffffu, rr, off);
+        sr += __shfl_xor_sync(0xffffffffu, sr, off);
+    }
+    if (threadIdx.x == 0) {
+        atomicAdd(&counters->radiance_rays, rr);
+        atomicAdd(&counters->shadow_rays, sr);
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_resolve(size_t n, const float* __restrict__ sum, float inv_spp, float* __restrict__ out) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = sum[i] * inv_spp;
+}
+
+// ---- host side -------------------------------------------------------------------
+struct WaveBuffers {
+    PathState st[2];
+    SurfaceState sf;
+    ShadowRays sh;
+};
+
+// lay the SoA arrays out in r->d_words (one allocation, `capacity` slots each)
+void layout_wave(B2ptRenderer* r, uint32_t capacity) {
+    if (r->wave_capacity == capacity && r->d_words.get()) return;
+    const size_t words = (size_t)(2 * kPathStateWords + kSurfaceStateWords + kShadowWords) * capacity;
+    r->d_words.alloc(words);
+    r->d_hits.alloc(capacity);
+    r->d_queues.alloc((size_t)4 * capacity);
+    r->d_wave_out.alloc((size_t)3 * capacity);
+    r->d_counts.alloc((size_t)5 * 100 + 1);   // active[<=100] + queued[<=99][4]
+    float* w = r->d_words.get();
+    auto take = [&]() { float* p = w; w += capacity; return p; };
+    for (int k = 0; k < 2; k++) {
+        PathState& s = r->st[k];
+        s.ox = take(); s.oy = take(); s.oz = take();
+        s.dx = take(); s.dy = take(); s.dz = take();
+        s.bx = take(); s.by = take(); s.bz = take();
+        s.rx = take(); s.ry = take(); s.rz = take();
+        s.id = reinterpret_cast<uint32_t*>(take());
+        s.seed = reinterpret_cast<uint32_t*>(take());
+    }
+    SurfaceState& f = r->surf;
+    f.px = take(); f.py = take(); f.pz = take();
+    f.gx = take(); f.gy = take(); f.gz = take();
+    f.nx = take(); f.ny = take(); f.nz = take();
+    f.ar = take(); f.ag = take(); f.ab = take();
+    f.rough = take();
+    f.info = reinterpret_cast<uint32_t*>(take());
+    ShadowRays& h = r->shadow;
+    h.ox = take(); h.oy = take(); h.oz = take();
+    h.dx = take(); h.dy = take(); h.dz = take();
+    h.tmax = take();
+    r->wave_capacity = capacity;
+}
+
+template <class Rng>
+void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwrite) {
+    cudaStream_t s = r->stream;
+    const int grid = r->sm_count * 8;
+    const DeviceScene sc = r->scene.view();
+    WaveCounts wc;
+    wc.active = r->d_counts.get();
+    wc.queued = r->d_counts.get() + 100;
+    LaunchCfg lc;
+    lc.stream = s;
+    lc.grid = grid;
+    lc.stats = r->cfg.collect_stats != 0;
+    lc.launch_counter = &r->kernel_launches;
+    auto count = [&](int k = 1) { r->kernel_launches += (uint64_t)k; };
+
+    r->d_counts.zero(s);
+    if (wp.max_bounces == 0) r->d_wave_out.zero(s);
+    k_raygen<Rng><<<grid, kThreads, 0, s>>>(wp, r->st[0], wc.active);
+    count();
+    const bool kinds[4] = {wp.mode == B2PT_BSDF_AUTO || wp.mode == B2PT_BSDF_CONDUCTOR, wp.mode == B2PT_BSDF_DIFFUSE,
+                           wp.mode == B2PT_BSDF_DIELECTRIC, wp.mode == B2PT_BSDF_AUTO || wp.mode == B2PT_BSDF_LAYERED};
+    for (int b = 0; b < wp.max_bounces; b++) {
+        const PathState& cur = r->st[b & 1];
+        const PathState& nxt = r->st[(b + 1) & 1];
+        launch_closest(lc, sc, cur, wc.active + b, 0.0f, 100.0f, r->d_hits.get(), r->d_counters.get());   // tmin 0, tmax 100 (:652)
+        k_surface<Rng><<<grid, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
+                                                 wc, (uint32_t)b, r->d_wave_out.get());
+        count();
+        if (wp.n_lights > 0)
+            launch_any(lc, sc, r->shadow, wc.active + b, 0.0f, r->surf.info, nullptr, r->d_counters.get());
+        uint32_t* q = r->d_queues.get();
+        const size_t cap = wp.capacity;
+        if (kinds[0]) { k_shade<kBsdfConductor, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 0 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); }
+        if (kinds[1]) { k_shade<kBsdfDiffuse, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 1 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); }
+        if (kinds[2]) { k_shade<kBsdfDielectric, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 2 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); }
+        if (kinds[3]) { k_shade<kBsdfLayered, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); }
+    }
+    k_accumulate<<<r->sm_count * 4, 256, 0, s>>>(wp, r->d_wave_out.get(), dst, overwrite ? 1 : 0, r->d_counters.get());
+    k_tally<<<1, 32, 0, s>>>(wc, wp.max_bounces, wp.n_lights > 0 ? 1 : 0, r->d_counters.get());
+    count(2);
+    B2PT_CUDA(cudaGetLastError());
+}
+
+}  // namespace
+
+void render_frames(B2ptRenderer* r, int spp, bool accumulate) {
+    B2PT_REQUIRE(r->width > 0 && r->height > 0, B2PT_E_STATE, "resize first");
+    B2PT_REQUIRE(r->have_camera, B2PT_E_STATE, "set_camera first");
+    B2PT_REQUIRE(accumulate || spp == 1, B2PT_E_INVALID, "Render traces exactly one sample per pixel");
+    const uint64_t n_pixels = (uint64_t)r->width * r->height;
+    int log2cap = r->cfg.wave_paths_log2;
+    if (log2cap <= 0) log2cap = 22;
+    B2PT_REQUIRE(log2cap >= 10 && log2cap <= 27, B2PT_E_INVALID, "wave_paths_log2 must be in [10, 27]");
+    const uint32_t capacity = 1u << log2cap;
+    layout_wave(r, capacity);
+
+    WaveParams wp;
+    wp.cam.position = v3(r->cam_pos[0], r->cam_pos[1], r->cam_pos[2]);
+    memcpy(wp.cam.inv_view, r->cam_inv_view, 64);
+    memcpy(wp.cam.inv_proj, r->cam_inv_proj, 64);
+    wp.cam.width = r->width;
+    wp.cam.height = r->height;
+    wp.lights = r->d_lights.get();
+    wp.n_lights = (int32_t)r->lights.size();
+    wp.max_bounces = r->cfg.max_bounces;
+    wp.mode = r->cfg.bsdf_mode;
+    wp.seed = r->cfg.seed;
+    wp.capacity = capacity;
+    float* dst = accumulate ? r->d_accum.get() : r->d_frame.get();
+
+    B2PT_CUDA(cudaEventRecord(r->ev0, r->stream));
+    const uint32_t tile = (uint32_t)std::min<uint64_t>(n_pixels, capacity);
+    const uint32_t spw_max = std::max<uint32_t>(1u, capacity / tile);
+    for (int s0 = 0; s0 < spp; s0 += (int)spw_max) {
+        wp.spw = (uint32_t)std::min<int>((int)spw_max, spp - s0);
+        wp.frame0 = r->frame_id + 1u + (uint32_t)s0;   // frame.id is pre-incremented (OptixRenderer.cpp:623)
+        for (uint64_t p0 = 0; p0 < n_pixels; p0 += tile) {
+            wp.p0 = (uint32_t)p0;
+            wp.np = (uint32_t)std::min<uint64_t>(tile, n_pixels - p0);
+            switch (r->cfg.rng_mode) {
+                case B2PT_RNG_LCG_DEVICE: enqueue_wave<LcgRng<false>>(r, wp, dst, !accumulate); break;
+                case B2PT_RNG_LCG_HOST: enqueue_wave<LcgRng<true>>(r, wp, dst, !accumulate); break;
+                default: enqueue_wave<PhiloxRng>(r, wp, dst, !accumulate); break;
+            }
+        }
+    }
+    B2PT_CUDA(cudaEventRecord(r->ev1, r->stream));
+    B2PT_CUDA(cudaEventSynchronize(r->ev1));
+    float ms = 0.0f;
+    B2PT_CUDA(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
+    r->device_ms_render += ms;
+    r->frame_id += (uint32_t)spp;
+    r->samples += n_pixels * (uint64_t)spp;
+    if (accumulate) r->spp_accumulated += (uint32_t)spp;
+}
+
+void resolve_mean(B2ptRenderer* r) {
+    const size_t n = (size_t)r->width * r->height * 3;
+    const float inv = r->spp_accumulated ? 1.0f / (float)r->spp_accumulated : 0.0f;
+    k_resolve<<<r->sm_count * 4, 256, 0, r->stream>>>(n, r->d_accum.get(), inv, r->d_frame.get());
+    r->kernel_launches++;
+    B2PT_CUDA(cudaGetLastError());
+}
+
+}  // namespace b2pt

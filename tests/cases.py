@@ -118,3 +118,53 @@ def bsdf_rows(seed=1, seeds_per_case=3, with_wi=True):
         wi /= np.linalg.norm(wi, axis=1, keepdims=True)
         out["wi"] = wi.astype(f32)
     return out
+
+
+# ---------------------------------------------------------------------------
+# whole-frame cases (reference-rendered goldens: tools/make_golden.py)
+# ---------------------------------------------------------------------------
+FRAME_W, FRAME_H, FRAME_BOUNCES, FRAME_N = 64, 36, 6, 2
+
+
+def checker_texture(n=16, alpha_holes=False):
+    t = np.zeros((n, n, 4), dtype=np.uint8)
+    yy, xx = np.mgrid[0:n, 0:n]
+    c = ((xx // 2 + yy // 2) % 2).astype(np.uint8)
+    t[..., 0] = 60 + 180 * c
+    t[..., 1] = 200 - 120 * c
+    t[..., 2] = 90 + (xx * 9) % 160
+    t[..., 3] = 255
+    if alpha_holes:
+        t[..., 3] = np.where((xx % 4 == 0) & (yy % 4 == 0), 40, 255)
+    return t
+
+
+def frame_scenes():
+    """name -> scene: the plain spheres scene, a half-metal variant (AUTO mixes
+    conductor and layered), and a textured variant (albedo + alpha cut-out,
+    normal map, metal-rough map)."""
+    plain = scenes.spheres_scene(segments=16, rings=8)
+    mixed = scenes.spheres_scene(segments=16, rings=8)
+    for k, me in enumerate(mixed["meshes"]):
+        me["metallic"] = (k % 3) * 0.5
+    tex = scenes.spheres_scene(segments=16, rings=8)
+    n = 16
+    yy, xx = np.mgrid[0:n, 0:n]
+    nm = np.zeros((n, n, 4), dtype=np.uint8)
+    nm[..., 0] = 128 + (20 * np.sin(xx * 0.8)).astype(np.int32)
+    nm[..., 1] = 128 + (20 * np.cos(yy * 0.8)).astype(np.int32)
+    nm[..., 2] = 235
+    nm[..., 3] = 255
+    mr = np.zeros((n, n, 4), dtype=np.uint8)
+    mr[..., 0] = np.where((xx + yy) % 2 == 0, 255, 0)
+    mr[..., 1] = 40 + 10 * ((xx * 3 + yy) % 16)
+    mr[..., 3] = 255
+    tex["textures"] = [checker_texture(n, alpha_holes=True), nm, mr]
+    for k, me in enumerate(tex["meshes"]):
+        if k % 2 == 0:
+            me["tex_albedo"] = 0
+        if k % 3 == 0:
+            me["tex_normal"] = 1
+        if k % 4 == 0:
+            me["tex_metal_rough"] = 2
+    return {"plain": plain, "mixed": mixed, "textured": tex}

@@ -220,7 +220,7 @@ void hostsim_bsdf_pdf(int bsdf, int64_t n, const float* roughness, const float* 
 }  // extern "C"
 
 // ---- whole frames: the wavefront stages (integrator.cuh) run per pixel --------
-#include "../../optixpathtracer_b200/csrc/integrator.cuh"
+#include "../../optixpathtracer_b200/csrc/alpha.cuh"
 
 namespace {
 
@@ -270,12 +270,13 @@ float3 trace_path(const HostScene& hs, const CameraParams& cam, int x, int y, ui
     ctx.sample = frame_id;
     ctx.lcg_state = RngIO<Rng>::first_state(ctx.pixel, frame_id);
     const HostTexFetch tex{hs.textures.data()};
+    const AlphaCutout<HostTexFetch> cutout{hs.view, tex};
     for (int bounce = 0; path_continues(pv.beta, bounce, max_bounces); bounce++) {
         ctx.bounce = (uint32_t)bounce;
         HitRecord hit;
         rays[0]++;
         if (!traverse<false, false>(hs.view.nodes, hs.view.tris, hs.view.n_nodes, pv.next_o, pv.next_d, 0.0f, 100.0f,
-                                    hit, nullptr))
+                                    hit, nullptr, cutout))
             break;   // __miss__radiance
         const float3 ray_d = pv.next_d;
         SurfacePoint sp;
@@ -289,7 +290,7 @@ float3 trace_path(const HostScene& hs, const CameraParams& cam, int x, int y, ui
             HitRecord sh;
             rays[1]++;
             visible = !traverse<true, false>(hs.view.nodes, hs.view.tris, hs.view.n_nodes, sp.sh_o, sp.sh_d, 0.0f,
-                                             sp.sh_tmax, sh, nullptr);
+                                             sp.sh_tmax, sh, nullptr, cutout);
         }
         int kind = mode - 1;
         if (mode == B2PT_BSDF_AUTO) kind = sp.conductor ? kBsdfConductor : kBsdfLayered;
