@@ -146,7 +146,8 @@ class OptixRenderer:
         """One sample per pixel, overwrite (OptixRenderer.cpp:617-647)."""
         if h_pixels is None:
             h_pixels = np.empty((self.height, self.width, 3), dtype=f32)
-        assert h_pixels.dtype == f32 and h_pixels.size == self.width * self.height * 3
+        # before the first Resize the call is a silent no-op like the reference's (:621)
+        assert h_pixels.dtype == f32 and (self.width == 0 or h_pixels.size == self.width * self.height * 3)
         check(self._h, self.lib.b2pt_render(self._h, _fp(h_pixels)))
         return h_pixels
 

@@ -33,6 +33,14 @@ NVCC_FLAGS = [
 ]
 
 
+# Shading code (BSDFs, surface reconstruction) is built without FMA contraction:
+# every a*b+c is then the same two IEEE roundings the reference's host build
+# performs, which keeps peaked microfacet lobes (alpha ~ 0.01, condition number
+# ~1e5) within the 1e-5 parity bar.  Traversal keeps FMA (its deciding test uses
+# explicit fp64 intrinsics and is exact by construction).
+PER_FILE_FLAGS = {"wavefront.cu": ["-fmad=false"], "bsdf_hooks.cu": ["-fmad=false"]}
+
+
 def _sources() -> list[Path]:
     return sorted(CSRC.glob("*.cu"))
 
@@ -44,6 +52,7 @@ def _fingerprint() -> str:
         h.update(p.name.encode())
         h.update(p.read_bytes())
     h.update(" ".join(NVCC_FLAGS).encode())
+    h.update(repr(sorted(PER_FILE_FLAGS.items())).encode())
     return h.hexdigest()
 
 
@@ -73,7 +82,7 @@ def build_lib(force: bool = False, verbose: bool = False) -> Path:
     for src in _sources():
         obj = objdir / (src.stem + ".o")
         objs.append(obj)
-        cmd = [nvcc, *NVCC_FLAGS, "-Xptxas", "-v", "-c", str(src), "-o", str(obj)]
+        cmd = [nvcc, *NVCC_FLAGS, *PER_FILE_FLAGS.get(src.name, []), "-Xptxas", "-v", "-c", str(src), "-o", str(obj)]
         log = open(objdir / (src.stem + ".log"), "w")
         procs.append((src, subprocess.Popen(cmd, stdout=log, stderr=subprocess.STDOUT), log))
     failed = []
