@@ -1,0 +1,390 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200-native path-tracing core.
+
+    python bench.py --gpus N --steps K --warmup W [--config c2] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Metric (BASELINE.json): Msamples/s — complete camera paths per second, whole job
+over all N GPUs.  Workload at N=1: BASELINE.json configs[1] (README "Conductor"
+scene, 1024x1024, depth 16, 256 spp); a STEP is one pass of the hot path over
+one batch = `spp_per_step` samples of every pixel (default 16, so 16 steps are
+the whole 256-spp config).  Multi-GPU = weak scaling: every rank renders its
+own spp_per_step samples per step (disjoint absolute sample indices, replicated
+scene/BVH) and the fp32 sums are combined with one NCCL reduce per step.
+
+One JSON line is printed by rank 0; see DESIGN.md "Measurement" for every key.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+f32 = np.float32
+
+CONFIGS = {
+    # id: (label, scene builder kwargs, W, H, spp, depth, bsdf_mode)
+    "c1": ("README Diffuse 512x512 64spp d8", dict(kind="spheres", metallic=0.0), 512, 512, 64, 8, "diffuse"),
+    "c2": ("README Conductor 1024x1024 256spp d16", dict(kind="spheres", metallic=1.0), 1024, 1024, 256, 16, "conductor"),
+    "c3": ("README Dielectric(bright) 1024x1024 1024spp d32", dict(kind="spheres", metallic=0.0, light_color=20.0),
+           1024, 1024, 1024, 32, "dielectric"),
+    "c4": ("README Layered 1920x1080 1024spp d8", dict(kind="spheres", metallic=0.0), 1920, 1080, 1024, 8, "layered"),
+    "c5": ("synthetic 2M-tri mixed 3840x2160 4096spp d8", dict(kind="terrain"), 3840, 2160, 4096, 8, "auto"),
+}
+
+
+def make_scene(spec):
+    from optixpathtracer_b200 import scenes
+    spec = dict(spec)
+    kind = spec.pop("kind")
+    return scenes.spheres_scene(**spec) if kind == "spheres" else scenes.terrain_scene()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (profiling recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.gpu)], stdout=open(self.path, "w"),
+                                         stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self) -> dict:
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in open(self.path).read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        os.unlink(self.path)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+def lights_array(lights):
+    from optixpathtracer_b200._lib import B2ptPointLight
+    arr = (B2ptPointLight * max(len(lights), 1))()
+    for i, (p, c) in enumerate(lights):
+        arr[i].position = (C.c_float * 3)(*np.asarray(p, dtype=f32))
+        arr[i].color = (C.c_float * 3)(*np.asarray(c, dtype=f32))
+    return arr
+
+
+def cpu_reference_run(scene, w, h, depth, mode_id, target_s: float, steps: int, warmup: int):
+    """Times the reference's own integrator + BSDF code compiled for the host
+    (oracle/_ref, OpenMP over all host cores; optixTrace served by the oracle's
+    host BVH, which is NOT reference code) on a bounded band of the full-size
+    frame.  Returns (Msamples/s, cores, sample description, Mrays/s, ms per step)."""
+    from tests.util import RefOracle, fp
+    from optixpathtracer_b200.api import _SceneMarshal
+    ro = RefOracle()
+    lib = ro.lib
+    m = _SceneMarshal(scene)
+    hnd = C.c_void_p(lib.ref_scene_create(C.byref(m.desc)))
+    pos, iv, ip = scene["camera"].launch_matrices(w, h)
+    arr = lights_array(scene["lights"])
+    cnt = (C.c_uint64 * 4)()
+    sec = C.c_double()
+
+    def rows_every(ystep, frame):
+        n_rows = len(range(0, h, ystep))
+        lib.ref_render_band(hnd, w, h, 0, h, ystep, fp(pos), fp(iv), fp(ip), arr, len(scene["lights"]), depth, mode_id,
+                            C.c_uint32(frame), 1, cnt, C.byref(sec))
+        return sec.value, cnt[0] + cnt[1], int(cnt[3]), n_rows
+
+    # calibrate on every 16th row (second run: threads and pages are warm), then size the row
+    # subset for ~target_s of CPU work per step
+    rows_every(16, 1)
+    t_cal, _, cores, n_cal = rows_every(16, 2)
+    want_rows = int(min(h, max(n_cal, n_cal * target_s / max(t_cal, 1e-6))))
+    ystep = max(1, h // want_rows)
+    for k in range(warmup):
+        rows_every(ystep, 100 + k)
+    tot_t, tot_rays, rows = 0.0, 0, 0
+    for k in range(steps):
+        t, rays, cores, rows = rows_every(ystep, 1 + k)
+        tot_t += t
+        tot_rays += rays
+    lib.ref_scene_destroy(hnd)
+    samples = rows * w * steps
+    desc = (f"every {ystep}. row ({rows} rows) of the {w}x{h} frame x 1 spp per step, {steps} steps, depth {depth}; reference "
+            f"integrator+BSDF code compiled for the host (g++ -O2 -fopenmp), traversal by the oracle's host BVH")
+    return samples / tot_t / 1e6, cores, desc, tot_rays / tot_t / 1e6, tot_t / steps * 1e3
+
+
+def run_reference(args, cfg):
+    label, spec, w, h, spp, depth, mode = cfg
+    from optixpathtracer_b200._lib import BSDF_NAMES
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    scene = make_scene(spec)
+    msps, cores, desc, mrays, ms_step = cpu_reference_run(scene, w, h, depth, BSDF_NAMES[mode], args.cpu_seconds,
+                                                          args.steps, args.warmup)
+    line = {"impl": "reference", "metric": "Msamples/s", "value": msps, "unit": "Msamples/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": label, "bsdf_mode": mode, "max_depth": depth},
+            "cpu_baseline": {"value": msps, "unit": "Msamples/s", "cores": cores, "kind": "reference", "sample": desc,
+                             "mrays_per_s": mrays},
+            "e2e": {"value": msps, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def algorithmic_bytes_per_ray(scene, w, h, depth, mode, spp=1):
+    """One stats pass of the same traversal on the same rays (collect_stats=1):
+    bytes a ray must read = nodes visited x node bytes + triangles tested x
+    triangle bytes + ray/hit I/O."""
+    from optixpathtracer_b200 import OptixRenderer
+    with OptixRenderer(None, scene, bsdf_mode=mode, rng_mode="philox", max_bounces=depth, collect_stats=True) as r:
+        r.Resize((w, h)); r.SetCamera(scene["camera"]); r.SetLights(scene["lights"])
+        r.RenderAccumulate(spp, download=False)
+        st = r.Stats()
+    rr, sr = max(st["radiance_rays"], 1), max(st["shadow_rays"], 1)
+    b_closest = (st["nodes_visited"] * st["node_bytes"] + st["triangles_tested"] * st["triangle_bytes"]) / rr + 48.0
+    b_any = (st["nodes_visited_shadow"] * st["node_bytes"] + st["triangles_tested_shadow"] * st["triangle_bytes"]) / sr + 36.0
+    return {"closest": b_closest, "any": b_any, "nodes_per_ray": st["nodes_visited"] / rr,
+            "tris_per_ray": st["triangles_tested"] / rr, "exact_per_ray": st["exact_tests"] / rr,
+            "nodes_per_shadow_ray": st["nodes_visited_shadow"] / sr, "tris_per_shadow_ray": st["triangles_tested_shadow"] / sr,
+            "rays_per_sample": (st["radiance_rays"] + st["shadow_rays"]) / max(st["samples"], 1)}
+
+
+class DevicePtr:
+    """Wraps a raw device pointer for torch.as_tensor (CUDA array interface)."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 3}
+
+
+def run_b2pt(args, cfg):
+    import torch
+    import torch.distributed as dist
+    from optixpathtracer_b200 import OptixRenderer
+
+    label, spec, w, h, spp_total, depth, mode = cfg
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the path-tracing core has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    n_gpus = world
+    spp = args.spp_per_step
+    scene = make_scene(spec)
+    n_px = w * h
+
+    r = OptixRenderer(None, scene, device=local, bsdf_mode=mode, rng_mode="philox", max_bounces=depth,
+                      wave_paths_log2=args.wave_log2)
+    r.Resize((w, h)); r.SetCamera(scene["camera"]); r.SetLights(scene["lights"])
+    build_ms = r.Stats()["device_ms_build"]
+    ptr, _ = r.AccumulationDevice()
+    acc = torch.as_tensor(DevicePtr(ptr, n_px * 3), device=f"cuda:{local}")
+    total = torch.zeros_like(acc)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step(k, frame_base):
+        # rank g renders absolute samples [base + g*spp, base + (g+1)*spp): disjoint Philox streams
+        r.ClearAccumulation()
+        r.SetFrameId(frame_base + (k * n_gpus + rank) * spp)
+        r.RenderAccumulate(spp, download=False)
+        if world > 1:
+            dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)     # one NCCL reduce of W*H*3 fp32 sums
+        if rank == 0:
+            total.add_(acc)
+        torch.cuda.current_stream().synchronize()
+
+    for k in range(args.warmup):
+        step(k, 1_000_000)
+    total.zero_()
+    r.ResetStats()
+    r.SetKernelTiming(True)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    for k in range(args.steps):
+        step(k, 0)
+    e1.record()
+    barrier()
+    wall_s = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else {}
+    dev_ms = e0.elapsed_time(e1)
+    st = r.Stats()
+    r.SetKernelTiming(False)
+    t = torch.tensor([dev_ms, st["device_ms_render"], wall_s * 1e3], device=f"cuda:{local}", dtype=torch.float64)
+    rays = torch.tensor([st["radiance_rays"], st["shadow_rays"], st["kernel_launches"]], device=f"cuda:{local}", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(rays, op=dist.ReduceOp.SUM)
+    dev_ms, render_ms, wall_ms = [float(x) for x in t.tolist()]
+    samples = n_px * spp * args.steps * n_gpus
+    value = samples / (dev_ms * 1e-3) / 1e6
+    mean_img = (total / float(spp * args.steps * n_gpus)).cpu().numpy() if rank == 0 else None
+
+    # ---- e2e: through the C-ABI with HOST buffers, every step: camera + lights H2D, result D2H -------
+    pinned = torch.empty(n_px * 3, dtype=torch.float32, pin_memory=True)
+    host_out = pinned.numpy().reshape(h, w, 3)
+    pos, iv, ip = scene["camera"].launch_matrices(w, h)
+    barrier()
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        r.SetCameraRaw(pos, iv, ip)
+        r.SetLights(scene["lights"])
+        r.ClearAccumulation()
+        r.SetFrameId((k * n_gpus + rank) * spp)
+        if world > 1:
+            r.RenderAccumulate(spp, download=False)
+            dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                pinned.copy_(acc.mul(1.0 / (spp * n_gpus)), non_blocking=False)
+            torch.cuda.current_stream().synchronize()
+        else:
+            r.RenderAccumulate(spp, out=host_out)                 # b2pt_render_accumulate: D2H inside the call
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], device=f"cuda:{local}", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = samples / float(te.item()) / 1e6
+    h2d = 12 + 64 + 64 + 24 * len(scene["lights"])
+    d2h = n_px * 12
+
+    if rank != 0:
+        r.close()
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (K5 closest-hit traversal) --------------------------------
+    peaks_path = ROOT / "MEASURED_PEAKS.json"
+    if peaks_path.exists():
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    bpr = algorithmic_bytes_per_ray(scene, w, h, depth, mode, spp=1)
+    ms_k, n_k = st["device_ms_kernel"], st["launches_kernel"]
+    closest_ms = max(ms_k[0], 1e-9)
+    achieved = st["radiance_rays"] * bpr["closest"] / (closest_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = ROOT / "profiles" / "traffic.json"
+    if tpath.exists():
+        try:
+            traffic = json.load(open(tpath)).get(args.config, {}).get("k_closest_dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    roofline = {"kernel": "k_closest (K5 closest-hit BVH traversal)", "bound": "hbm", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "bytes_per_ray": bpr["closest"], "nodes_per_ray": bpr["nodes_per_ray"], "tris_per_ray": bpr["tris_per_ray"],
+                "bytes_per_launch": st["radiance_rays"] * bpr["closest"] / max(n_k[0], 1),
+                "ms_per_launch": closest_ms / max(n_k[0], 1), "launches": n_k[0],
+                "share_of_step": {"closest": ms_k[0] / render_ms, "any": ms_k[1] / render_ms, "surface": ms_k[2] / render_ms,
+                                  "shade": ms_k[3] / render_ms, "other": ms_k[4] / render_ms},
+                "shadow": {"achieved": st["shadow_rays"] * bpr["any"] / (max(ms_k[1], 1e-9) * 1e-3) / 1e9,
+                           "bytes_per_ray": bpr["any"]},
+                "note": "scene BVH+triangles are L2-resident for the README scenes (16 MB < 126 MB L2): the HBM fraction can "
+                        "exceed what DRAM traffic shows; see DESIGN.md"}
+
+    cpu = None
+    if n_gpus == 1 and not args.no_cpu_baseline:
+        from optixpathtracer_b200._lib import BSDF_NAMES
+        try:
+            v, cores, desc, mrays, _ = cpu_reference_run(scene, w, h, depth, BSDF_NAMES[mode], args.cpu_seconds, 1, 0)
+            cpu = {"value": v, "unit": "Msamples/s", "cores": cores, "kind": "reference", "sample": desc, "mrays_per_s": mrays}
+        except Exception as e:  # the checker library is missing: say so, do not invent a number
+            cpu = {"value": None, "unit": "Msamples/s", "cores": 0, "kind": "reference", "sample": f"unavailable: {e}"}
+
+    line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": n_gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": label, "config_id": args.config, "width": w, "height": h, "spp_per_step_per_gpu": spp,
+                       "spp_config": spp_total, "max_depth": depth, "bsdf_mode": mode, "rng": "philox",
+                       "triangles": st["n_triangles"], "bvh_nodes": st["n_nodes"], "bvh_build_ms": build_ms,
+                       "scene_device_bytes": st["scene_device_bytes"], "wave_paths_log2": args.wave_log2 or 22,
+                       "parallelism": f"spp-split x{n_gpus}, replicated BVH, one NCCL reduce per step" if n_gpus > 1 else "single GPU",
+                       "l2": "path state of a wave (~1 GB SoA) exceeds L2; the 16 MB BVH is L2-resident by nature of the workload"},
+            "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+            "gpu_launches": int(rays[2].item()),
+            "mrays_per_s": float(rays[0].item() + rays[1].item()) / (dev_ms * 1e-3) / 1e6,
+            "rays_per_sample": bpr["rays_per_sample"],
+            "device_ms_render_max": render_ms, "wall_ms": wall_ms,
+            "image_mean": float(mean_img.mean()), "image_finite": bool(np.isfinite(mean_img).all()),
+            "nan_samples": st["nan_pixels"],
+            "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(line))
+    r.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b2pt", choices=["b2pt", "reference"])
+    ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
+    ap.add_argument("--spp-per-step", type=int, default=16)
+    ap.add_argument("--wave-log2", type=int, default=0)
+    ap.add_argument("--cpu-seconds", type=float, default=None, help="CPU work per reference step / baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.cpu_seconds is None:
+        args.cpu_seconds = 5.0 if args.impl == "reference" else 15.0
+    cfg = CONFIGS[args.config]
+    if args.impl == "reference":
+        run_reference(args, cfg)
+    else:
+        run_b2pt(args, cfg)
+
+
+if __name__ == "__main__":
+    main()

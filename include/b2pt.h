@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B2PT_ABI_VERSION 1
+#define B2PT_ABI_VERSION 2
 
 /* ---- status codes ------------------------------------------------------ */
 enum {
@@ -140,6 +140,18 @@ typedef struct B2ptStats {
     int32_t  node_bytes;
     int32_t  triangle_bytes;
     int64_t  scene_device_bytes;
+    /* shadow-ray share of the traversal counters (only with collect_stats);
+     * nodes_visited / triangles_tested / exact_tests above are the closest-hit
+     * share */
+    uint64_t nodes_visited_shadow;
+    uint64_t triangles_tested_shadow;
+    uint64_t exact_tests_shadow;
+    /* per-kernel-class device time of render calls, CUDA events on the
+     * renderer's stream (only while b2pt_set_kernel_timing is on):
+     * [0] K5 closest-hit traversal, [1] K8 any-hit traversal, [2] K6 surface,
+     * [3] K7 shade (all BSDFs), [4] K4 raygen + K9 accumulate + bookkeeping   */
+    double   device_ms_kernel[5];
+    uint64_t launches_kernel[5];
 } B2ptStats;
 
 typedef struct B2ptRenderer B2ptRenderer;
@@ -199,6 +211,9 @@ int b2pt_get_accumulation_device(B2ptRenderer* r, float** d_rgb_sum, uint32_t* s
 int b2pt_download_accumulation(B2ptRenderer* r, float* h_rgb_sum, uint32_t* spp_accumulated);
 int b2pt_upload_accumulation(B2ptRenderer* r, const float* h_rgb_sum, uint32_t spp_accumulated);
 
+/* Record a CUDA event after every kernel of the render calls and attribute the
+ * elapsed device time per kernel class (B2ptStats.device_ms_kernel).         */
+int b2pt_set_kernel_timing(B2ptRenderer* r, int32_t on);
 int b2pt_get_stats(const B2ptRenderer* r, B2ptStats* out);
 int b2pt_reset_stats(B2ptRenderer* r);
 

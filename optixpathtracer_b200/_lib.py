@@ -62,7 +62,10 @@ class B2ptStats(C.Structure):
                 ("kernel_launches", C.c_uint64), ("device_ms_render", C.c_double),
                 ("device_ms_build", C.c_double), ("n_triangles", C.c_int32), ("n_nodes", C.c_int32),
                 ("node_bytes", C.c_int32), ("triangle_bytes", C.c_int32),
-                ("scene_device_bytes", C.c_int64)]
+                ("scene_device_bytes", C.c_int64),
+                ("nodes_visited_shadow", C.c_uint64), ("triangles_tested_shadow", C.c_uint64),
+                ("exact_tests_shadow", C.c_uint64),
+                ("device_ms_kernel", C.c_double * 5), ("launches_kernel", C.c_uint64 * 5)]
 
 
 # name -> (restype, argtypes); exactly the symbols include/b2pt.h declares.
@@ -88,6 +91,7 @@ SIGNATURES = {
     "b2pt_get_accumulation_device": (C.c_int, [_H, C.POINTER(C.c_void_p), c_uint32_p]),
     "b2pt_download_accumulation": (C.c_int, [_H, c_float_p, c_uint32_p]),
     "b2pt_upload_accumulation": (C.c_int, [_H, c_float_p, C.c_uint32]),
+    "b2pt_set_kernel_timing": (C.c_int, [_H, C.c_int32]),
     "b2pt_get_stats": (C.c_int, [_H, C.POINTER(B2ptStats)]),
     "b2pt_reset_stats": (C.c_int, [_H]),
     "b2pt_trace_closest": (C.c_int, [_H, C.c_int64, c_float_p, c_float_p, C.c_float, C.c_float,

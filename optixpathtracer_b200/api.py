@@ -199,7 +199,14 @@ class OptixRenderer:
     def Stats(self) -> dict:
         s = B2ptStats()
         check(self._h, self.lib.b2pt_get_stats(self._h, C.byref(s)))
-        return {k: getattr(s, k) for k, _ in B2ptStats._fields_}
+        out = {}
+        for k, _ in B2ptStats._fields_:
+            v = getattr(s, k)
+            out[k] = list(v) if hasattr(v, "__len__") else v
+        return out
+
+    def SetKernelTiming(self, on: bool = True):
+        check(self._h, self.lib.b2pt_set_kernel_timing(self._h, int(on)))
 
     def ResetStats(self):
         check(self._h, self.lib.b2pt_reset_stats(self._h))

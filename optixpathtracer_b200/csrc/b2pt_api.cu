@@ -107,6 +107,7 @@ void b2pt_destroy(B2ptRenderer* r) {
     cudaSetDevice(r->device);
     if (r->stream) cudaStreamSynchronize(r->stream);
     r->scene.free_textures();
+    for (cudaEvent_t e : r->timing_events) cudaEventDestroy(e);
     if (r->ev0) cudaEventDestroy(r->ev0);
     if (r->ev1) cudaEventDestroy(r->ev1);
     if (r->stream) cudaStreamDestroy(r->stream);
@@ -287,7 +288,20 @@ int b2pt_get_stats(const B2ptRenderer* rc, B2ptStats* out) {
         out->node_bytes = (int32_t)sizeof(BvhNode2);
         out->triangle_bytes = (int32_t)sizeof(TriRecord);
         out->scene_device_bytes = r->scene.device_bytes();
+        out->nodes_visited_shadow = c.nodes_any;
+        out->triangles_tested_shadow = c.tris_any;
+        out->exact_tests_shadow = c.exact_any;
+        for (int k = 0; k < 5; k++) {
+            out->device_ms_kernel[k] = r->ms_kernel[k];
+            out->launches_kernel[k] = r->launches_kernel_cls[k];
+        }
     });
+}
+
+int b2pt_set_kernel_timing(B2ptRenderer* r, int32_t on) {
+    if (!r) return B2PT_E_INVALID;
+    r->kernel_timing = on != 0;
+    return B2PT_OK;
 }
 
 int b2pt_reset_stats(B2ptRenderer* r) {
@@ -298,6 +312,7 @@ int b2pt_reset_stats(B2ptRenderer* r) {
         r->kernel_launches = 0;
         r->hook_radiance_rays = r->hook_shadow_rays = 0;
         r->device_ms_render = 0.0;
+        for (int k = 0; k < 5; k++) { r->ms_kernel[k] = 0.0; r->launches_kernel_cls[k] = 0; }
         B2PT_CUDA(cudaStreamSynchronize(r->stream));
     });
 }

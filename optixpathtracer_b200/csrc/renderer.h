@@ -54,5 +54,13 @@ struct B2ptRenderer {
     uint64_t hook_radiance_rays = 0, hook_shadow_rays = 0;   // rays traced by the parity hooks
     double device_ms_render = 0.0;
 
+    // per-kernel-class timing (b2pt_set_kernel_timing)
+    bool kernel_timing = false;
+    std::vector<cudaEvent_t> timing_events;   // pool, reused by every render call
+    std::vector<int> timing_tags;             // class of the kernel that ended at event i+1
+    size_t timing_used = 0;
+    double ms_kernel[5] = {0, 0, 0, 0, 0};
+    uint64_t launches_kernel_cls[5] = {0, 0, 0, 0, 0};
+
     void set_error(const std::string& m) { last_error = m; }
 };

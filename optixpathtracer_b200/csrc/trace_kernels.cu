@@ -60,9 +60,9 @@ k_any(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, floa
         if (occluded) occluded[i] = occ ? 1 : 0;
     }
     if (STATS) {
-        atomicAdd(&counters->nodes, (unsigned long long)ts.nodes);
-        atomicAdd(&counters->tris, (unsigned long long)ts.tris);
-        atomicAdd(&counters->exact, (unsigned long long)ts.exact);
+        atomicAdd(&counters->nodes_any, (unsigned long long)ts.nodes);
+        atomicAdd(&counters->tris_any, (unsigned long long)ts.tris);
+        atomicAdd(&counters->exact_any, (unsigned long long)ts.exact);
     }
 }
 

@@ -314,32 +314,51 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
     lc.stats = r->cfg.collect_stats != 0;
     lc.launch_counter = &r->kernel_launches;
     auto count = [&](int k = 1) { r->kernel_launches += (uint64_t)k; };
+    // with kernel timing on, an event closes every kernel; elapsed(i, i+1) belongs to class tag[i]
+    auto mark = [&](int cls, bool is_launch = true) {
+        if (is_launch) r->launches_kernel_cls[cls]++;
+        if (!r->kernel_timing) return;
+        if (r->timing_used == r->timing_events.size()) {
+            cudaEvent_t e;
+            B2PT_CUDA(cudaEventCreate(&e));
+            r->timing_events.push_back(e);
+        }
+        B2PT_CUDA(cudaEventRecord(r->timing_events[r->timing_used++], s));
+        r->timing_tags.push_back(cls);
+    };
+    mark(kClsOther, false);   // opening event of the wave
 
     r->d_counts.zero(s);
     if (wp.max_bounces == 0) r->d_wave_out.zero(s);
     k_raygen<Rng><<<grid, kThreads, 0, s>>>(wp, r->st[0], wc.active);
     count();
+    mark(kClsOther);
     const bool kinds[4] = {wp.mode == B2PT_BSDF_AUTO || wp.mode == B2PT_BSDF_CONDUCTOR, wp.mode == B2PT_BSDF_DIFFUSE,
                            wp.mode == B2PT_BSDF_DIELECTRIC, wp.mode == B2PT_BSDF_AUTO || wp.mode == B2PT_BSDF_LAYERED};
     for (int b = 0; b < wp.max_bounces; b++) {
         const PathState& cur = r->st[b & 1];
         const PathState& nxt = r->st[(b + 1) & 1];
         launch_closest(lc, sc, cur, wc.active + b, 0.0f, 100.0f, r->d_hits.get(), r->d_counters.get());   // tmin 0, tmax 100 (:652)
+        mark(kClsClosest);
         k_surface<Rng><<<grid, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
                                                  wc, (uint32_t)b, r->d_wave_out.get());
         count();
-        if (wp.n_lights > 0)
+        mark(kClsSurface);
+        if (wp.n_lights > 0) {
             launch_any(lc, sc, r->shadow, wc.active + b, 0.0f, r->surf.info, nullptr, r->d_counters.get());
+            mark(kClsAny);
+        }
         uint32_t* q = r->d_queues.get();
         const size_t cap = wp.capacity;
-        if (kinds[0]) { k_shade<kBsdfConductor, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 0 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); }
-        if (kinds[1]) { k_shade<kBsdfDiffuse, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 1 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); }
-        if (kinds[2]) { k_shade<kBsdfDielectric, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 2 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); }
-        if (kinds[3]) { k_shade<kBsdfLayered, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); }
+        if (kinds[0]) { k_shade<kBsdfConductor, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 0 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+        if (kinds[1]) { k_shade<kBsdfDiffuse, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 1 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+        if (kinds[2]) { k_shade<kBsdfDielectric, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 2 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+        if (kinds[3]) { k_shade<kBsdfLayered, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
     }
     k_accumulate<<<r->sm_count * 4, 256, 0, s>>>(wp, r->d_wave_out.get(), dst, overwrite ? 1 : 0, r->d_counters.get());
     k_tally<<<1, 32, 0, s>>>(wc, wp.max_bounces, wp.n_lights > 0 ? 1 : 0, r->d_counters.get());
     count(2);
+    mark(kClsOther);
     B2PT_CUDA(cudaGetLastError());
 }
 
@@ -370,6 +389,8 @@ void render_frames(B2ptRenderer* r, int spp, bool accumulate) {
     wp.capacity = capacity;
     float* dst = accumulate ? r->d_accum.get() : r->d_frame.get();
 
+    r->timing_used = 0;
+    r->timing_tags.clear();
     B2PT_CUDA(cudaEventRecord(r->ev0, r->stream));
     const uint32_t tile = (uint32_t)std::min<uint64_t>(n_pixels, capacity);
     const uint32_t spw_max = std::max<uint32_t>(1u, capacity / tile);
@@ -391,6 +412,13 @@ void render_frames(B2ptRenderer* r, int spp, bool accumulate) {
     float ms = 0.0f;
     B2PT_CUDA(cudaEventElapsedTime(&ms, r->ev0, r->ev1));
     r->device_ms_render += ms;
+    for (size_t i = 1; i < r->timing_used; i++) {
+        // tag[i] is the class of the kernel that ended at event i; the opening mark of a wave is
+        // tagged kClsOther and collects the memset before raygen
+        float dt = 0.0f;
+        B2PT_CUDA(cudaEventElapsedTime(&dt, r->timing_events[i - 1], r->timing_events[i]));
+        r->ms_kernel[r->timing_tags[i]] += dt;
+    }
     r->frame_id += (uint32_t)spp;
     r->samples += n_pixels * (uint64_t)spp;
     if (accumulate) r->spp_accumulated += (uint32_t)spp;

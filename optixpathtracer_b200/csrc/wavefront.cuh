@@ -55,7 +55,9 @@ constexpr int kShadowWords = 7;
 
 struct TraceCounters {
     unsigned long long nodes, tris, exact, radiance_rays, shadow_rays, nan_samples;
+    unsigned long long nodes_any, tris_any, exact_any;
 };
+enum KernelClass : int { kClsClosest = 0, kClsAny = 1, kClsSurface = 2, kClsShade = 3, kClsOther = 4, kClsCount = 5 };
 
 // ---- launchers (wavefront.cu / trace_kernels.cu) ---------------------------
 struct LaunchCfg {

@@ -327,10 +327,10 @@ int64_t ref_scene_triangles(void* h, float* soup_out) {
 //             (kept out of the mean; the GL path would poison the pixel and
 //             WriteEXR zeroes it, WriteImage.cpp:52-55), [3] threads used
 // mode = B2PT_BSDF_*; restated = 1 forces ref_closesthit_mode even in AUTO.
-void ref_render(void* h, int width, int height, const float* cam_pos, const float* inv_view,
-                const float* inv_proj, const B2ptPointLight* lights, int n_lights, int max_bounces,
-                int mode, int restated, uint32_t frame_first, int n_frames, float* mean_out,
-                float* frames_out, uint64_t* counters) {
+static void render_impl(void* h, int width, int height, int y0, int y1, int ystep, const float* cam_pos, const float* inv_view,
+                        const float* inv_proj, const B2ptPointLight* lights, int n_lights, int max_bounces,
+                        int mode, int restated, uint32_t frame_first, int n_frames, float* mean_out,
+                        float* frames_out, uint64_t* counters, double* seconds) {
     RefScene* sc = static_cast<RefScene*>(h);
     std::vector<glm::vec3> color((size_t)width * height);
     std::vector<PointLight> pl((size_t)std::max(n_lights, 1));
@@ -350,6 +350,7 @@ void ref_render(void* h, int width, int height, const float* cam_pos, const floa
     uint64_t rr = 0, sr = 0, nans = 0;
     int threads = 1;
     if (mean_out) memset(mean_out, 0, (size_t)width * height * 12);
+    const double t_begin = omp_get_wtime();
     for (int f = 0; f < n_frames; f++) {
         optixLaunchParams.frame.id = frame_first + (uint32_t)f;
 #pragma omp parallel reduction(+ : rr, sr)
@@ -361,7 +362,7 @@ void ref_render(void* h, int width, int height, const float* cam_pos, const floa
 #pragma omp single
             threads = omp_get_num_threads();
 #pragma omp for schedule(dynamic, 1)
-            for (int y = 0; y < height; y++)
+            for (int y = y0; y < y1; y += ystep)
                 for (int x = 0; x < width; x++) {
                     g_shim.launch_index = make_uint3((unsigned)x, (unsigned)y, 0);
                     __raygen__renderFrame();
@@ -385,6 +386,7 @@ void ref_render(void* h, int width, int height, const float* cam_pos, const floa
             }
         }
     }
+    if (seconds) *seconds = omp_get_wtime() - t_begin;
     if (counters) {
         counters[0] = rr;
         counters[1] = sr;
@@ -394,6 +396,25 @@ void ref_render(void* h, int width, int height, const float* cam_pos, const floa
 }
 
 }  // extern "C"
+
+extern "C" {
+void ref_render(void* h, int width, int height, const float* cam_pos, const float* inv_view,
+                const float* inv_proj, const B2ptPointLight* lights, int n_lights, int max_bounces,
+                int mode, int restated, uint32_t frame_first, int n_frames, float* mean_out,
+                float* frames_out, uint64_t* counters) {
+    render_impl(h, width, height, 0, height, 1, cam_pos, inv_view, inv_proj, lights, n_lights, max_bounces, mode,
+                restated, frame_first, n_frames, mean_out, frames_out, counters, nullptr);
+}
+// Rows y0, y0 + ystep, ... < y1 only (the timed CPU baseline of bench.py renders a
+// bounded, evenly spread subset of the rows of the full-size frame);
+// *seconds = wall time of the frame loop.
+void ref_render_band(void* h, int width, int height, int y0, int y1, int ystep, const float* cam_pos, const float* inv_view,
+                     const float* inv_proj, const B2ptPointLight* lights, int n_lights, int max_bounces,
+                     int mode, uint32_t frame_first, int n_frames, uint64_t* counters, double* seconds) {
+    render_impl(h, width, height, y0, y1, ystep < 1 ? 1 : ystep, cam_pos, inv_view, inv_proj, lights, n_lights, max_bounces, mode, 0,
+                frame_first, n_frames, nullptr, nullptr, counters, seconds);
+}
+}
 
 // ---------------------------------------------------------------------------
 // BSDF entry points: the reference's functions, one call per row.
