@@ -126,10 +126,12 @@ def cpu_reference_run(scene, w, h, depth, mode_id, target_s: float, steps: int, 
     cnt = (C.c_uint64 * 4)()
     sec = C.c_double()
 
+    n_frames = 1
+
     def rows_every(ystep, frame):
         n_rows = len(range(0, h, ystep))
         lib.ref_render_band(hnd, w, h, 0, h, ystep, fp(pos), fp(iv), fp(ip), arr, len(scene["lights"]), depth, mode_id,
-                            C.c_uint32(frame), 1, cnt, C.byref(sec))
+                            C.c_uint32(frame), n_frames, cnt, C.byref(sec))
         return sec.value, cnt[0] + cnt[1], int(cnt[3]), n_rows
 
     # calibrate on every 16th row (second run: threads and pages are warm), then size the row
@@ -138,16 +140,18 @@ def cpu_reference_run(scene, w, h, depth, mode_id, target_s: float, steps: int, 
     t_cal, _, cores, n_cal = rows_every(16, 2)
     want_rows = int(min(h, max(n_cal, n_cal * target_s / max(t_cal, 1e-6))))
     ystep = max(1, h // want_rows)
+    if ystep == 1:   # a whole frame is cheaper than the target: several samples per pixel per step
+        n_frames = int(max(1, min(256, target_s / max(t_cal * h / n_cal, 1e-6))))
     for k in range(warmup):
         rows_every(ystep, 100 + k)
     tot_t, tot_rays, rows = 0.0, 0, 0
     for k in range(steps):
-        t, rays, cores, rows = rows_every(ystep, 1 + k)
+        t, rays, cores, rows = rows_every(ystep, 1 + k * n_frames)
         tot_t += t
         tot_rays += rays
     lib.ref_scene_destroy(hnd)
-    samples = rows * w * steps
-    desc = (f"every {ystep}. row ({rows} rows) of the {w}x{h} frame x 1 spp per step, {steps} steps, depth {depth}; reference "
+    samples = rows * w * steps * n_frames
+    desc = (f"every {ystep}. row ({rows} rows) of the {w}x{h} frame x {n_frames} spp per step, {steps} steps, depth {depth}; reference "
             f"integrator+BSDF code compiled for the host (g++ -O2 -fopenmp), traversal by the oracle's host BVH")
     return samples / tot_t / 1e6, cores, desc, tot_rays / tot_t / 1e6, tot_t / steps * 1e3
 

@@ -20,7 +20,11 @@ for b in (1, 2, 3, 4):
     ok, sf, wi, pdf, fl, so = gpu_bsdf_sample(b, g)
     m = (ok == g[f"s{b}_ok"]) & (fl == g[f"s{b}_flags"]) & (so == g[f"s{b}_seed"])
     print(f"s{b}: branch flips {(~m).sum()}")
-    for name, got, ref in (("f", sf, g[f"s{b}_f"]), ("wi", wi, g[f"s{b}_wi"]), ("pdf", pdf[:, None], g[f"s{b}_pdf"][:, None])):
+    with np.errstate(all="ignore"):
+        wg = sf * np.abs(wi[:, 2:3]) / pdf[:, None]
+        wr = g[f"s{b}_f"] * np.abs(g[f"s{b}_wi"][:, 2:3]) / g[f"s{b}_pdf"][:, None]
+    wg, wr = np.nan_to_num(wg), np.nan_to_num(wr)
+    for name, got, ref in (("f", sf, g[f"s{b}_f"]), ("wi", wi, g[f"s{b}_wi"]), ("pdf", pdf[:, None], g[f"s{b}_pdf"][:, None]), ("weight", wg, wr)):
         e = (np.abs(got - ref) / (1e-6 + 1e-5 * np.abs(ref))).max(1)
         e = np.where(m, e, 0)
         bad = np.nonzero(e > 1)[0]
