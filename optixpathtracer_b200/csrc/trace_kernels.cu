@@ -8,6 +8,9 @@
 #include "wavefront.cuh"
 #include "traverse.cuh"
 #include "alpha.cuh"
+#include "trace_persistent.cuh"
+
+#include <cstdlib>
 
 namespace b2pt {
 
@@ -66,12 +69,100 @@ k_any(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, floa
     }
 }
 
+// ---- warp-persistent variants (trace_persistent.cuh) ---------------------------
+struct ClosestIo {
+    PathState st;
+    HitRecord* hits;
+    __device__ __forceinline__ bool load(uint32_t i, float3& o, float3& d, float& tmax_out) const {
+        o = v3(st.ox[i], st.oy[i], st.oz[i]);
+        d = v3(st.dx[i], st.dy[i], st.dz[i]);
+        tmax_out = tmax;
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, const HitRecord& h, bool) const {
+        reinterpret_cast<float4*>(hits)[i] = make_float4(__uint_as_float(h.tri), h.t, h.u, h.v);
+    }
+    float tmax;
+};
+struct AnyIo {
+    ShadowRays sh;
+    uint32_t* info;
+    uint8_t* occluded;
+    __device__ __forceinline__ bool load(uint32_t i, float3& o, float3& d, float& tmax_out) const {
+        tmax_out = sh.tmax[i];
+        if (!(tmax_out >= 0.0f)) return false;   // no shadow ray for this slot
+        o = v3(sh.ox[i], sh.oy[i], sh.oz[i]);
+        d = v3(sh.dx[i], sh.dy[i], sh.dz[i]);
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, const HitRecord&, bool occ) const {
+        if (info && !occ) info[i] |= kInfoVisible;
+        if (occluded) occluded[i] = occ ? 1 : 0;
+    }
+};
+
+constexpr int kRefillLanes = 8;
+
+template <bool STATS, bool ALPHA>
+__global__ void __launch_bounds__(kTraceThreads)
+k_closest_p(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active, float tmin, float tmax,
+            HitRecord* __restrict__ hits, TraceCounters* counters) {
+    TraceStats ts = {0, 0, 0};
+    const ClosestIo io{st, hits, tmax};
+    if (ALPHA)
+        trace_persistent<false, STATS, kRefillLanes>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io,
+                                                     AlphaCutout<DeviceTexFetch>{sc, DeviceTexFetch{sc.textures}}, ts);
+    else
+        trace_persistent<false, STATS, kRefillLanes>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io, AcceptAllHits(), ts);
+    if (STATS) {
+        atomicAdd(&counters->nodes, (unsigned long long)ts.nodes);
+        atomicAdd(&counters->tris, (unsigned long long)ts.tris);
+        atomicAdd(&counters->exact, (unsigned long long)ts.exact);
+    }
+}
+
+template <bool STATS, bool ALPHA>
+__global__ void __launch_bounds__(kTraceThreads)
+k_any_p(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, float tmin,
+        uint32_t* __restrict__ info, uint8_t* __restrict__ occluded, TraceCounters* counters) {
+    TraceStats ts = {0, 0, 0};
+    const AnyIo io{sh, info, occluded};
+    if (ALPHA)
+        trace_persistent<true, STATS, kRefillLanes>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io,
+                                                    AlphaCutout<DeviceTexFetch>{sc, DeviceTexFetch{sc.textures}}, ts);
+    else
+        trace_persistent<true, STATS, kRefillLanes>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io, AcceptAllHits(), ts);
+    if (STATS) {
+        atomicAdd(&counters->nodes_any, (unsigned long long)ts.nodes);
+        atomicAdd(&counters->tris_any, (unsigned long long)ts.tris);
+        atomicAdd(&counters->exact_any, (unsigned long long)ts.exact);
+    }
+}
+
+// B2PT_TRAVERSAL=0 selects the first (thread-per-ray) kernels, for A/B measurements
+bool use_persistent() {
+    static const bool v = [] { const char* e = getenv("B2PT_TRAVERSAL"); return !(e && e[0] == '0'); }();
+    return v;
+}
+
 }  // namespace
 
 void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState& st,
                     const uint32_t* n_active, float tmin, float tmax, HitRecord* hits,
                     TraceCounters* counters) {
     const bool alpha = sc.any_alpha_texture != 0;
+    if (use_persistent()) {
+        if (lc.stats && alpha)
+            k_closest_p<true, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters);
+        else if (lc.stats)
+            k_closest_p<true, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters);
+        else if (alpha)
+            k_closest_p<false, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters);
+        else
+            k_closest_p<false, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters);
+        if (lc.launch_counter) ++*lc.launch_counter;
+        return;
+    }
     if (lc.stats && alpha)
         k_closest<true, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters);
     else if (lc.stats)
@@ -87,6 +178,18 @@ void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh
                 const uint32_t* n_active, float tmin, uint32_t* info, uint8_t* occluded,
                 TraceCounters* counters) {
     const bool alpha = sc.any_alpha_texture != 0;
+    if (use_persistent()) {
+        if (lc.stats && alpha)
+            k_any_p<true, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters);
+        else if (lc.stats)
+            k_any_p<true, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters);
+        else if (alpha)
+            k_any_p<false, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters);
+        else
+            k_any_p<false, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters);
+        if (lc.launch_counter) ++*lc.launch_counter;
+        return;
+    }
     if (lc.stats && alpha)
         k_any<true, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters);
     else if (lc.stats)

@@ -1,0 +1,181 @@
+// trace_persistent.cuh — warp-persistent BVH traversal (the K5/K8 kernel bodies).
+//
+// Same hit contract and the same per-triangle / per-box arithmetic as
+// traverse() in traverse.cuh (which stays the single-thread statement the CPU
+// test tier runs); what changes is how a WARP is kept busy — the first kernel
+// of this round ran at 6-13 active lanes of 32 (profiles/r01_k_closest_full_
+// summary.csv):
+//
+//   * rays are not bound to threads: a warp owns an interleaved sequence of
+//     64-ray chunks and a lane that finishes its ray takes the next one as soon
+//     as kRefill lanes are idle (warp-uniform cursor + ballot/popc ranks; no
+//     atomics, the assignment is deterministic);
+//   * while-while: all lanes descend internal nodes together, then all lanes
+//     test their triangles together; a lane that reaches a leaf early postpones
+//     it and keeps descending, so the fp64-backed triangle code runs with many
+//     lanes active instead of one or two.
+//
+// Traversal order differs from traverse(), the result cannot: the closest hit
+// is the minimum fp64 t with ties broken by primitive id, and any-hit is an
+// existence test.
+#pragma once
+
+#include "traverse.cuh"
+
+namespace b2pt {
+
+constexpr uint32_t kFullMask = 0xffffffffu;
+constexpr uint32_t kRayChunk = 64;
+
+// Io: bool load(uint32_t i, float3& o, float3& d, float& tmax)   (false: slot carries no ray)
+//     void store(uint32_t i, const HitRecord& h, bool occluded)
+template <bool ANY, bool STATS, int kRefill, class Accept, class Io>
+__device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ nodes,
+                                                 const TriRecord* __restrict__ tris, int n_nodes,
+                                                 uint32_t n_rays, float tmin, const Io& io,
+                                                 const Accept& accept, TraceStats& ts) {
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lanes_lt = (1u << lane) - 1u;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
+    uint32_t seq = 0;   // warp-uniform: next position of this warp's ray sequence
+
+    // per-lane ray state
+    int node = kStackSentinel;   // sentinel = idle
+    int pend = 0;                // postponed leaf (< 0) or none
+    bool has_ray = false, occluded = false;
+    uint32_t ri = 0;
+    RaySetup r;
+    r.o = r.d = r.idir = v3(0.0f);
+    r.d_l1 = 0.0f;
+    float best32 = 0.0f;
+    double best_t = 0.0, tmax_d = 0.0;
+    const double tmin_d = (double)tmin;
+    uint32_t best_prim = 0xFFFFFFFFu;
+    HitRecord hit;
+    hit.tri = kHitMiss;
+    hit.t = hit.u = hit.v = 0.0f;
+    int stack[kStackSize];
+    int sp = 0;
+
+    while (true) {
+        // ---- finished lanes publish; idle lanes take new rays -----------------
+        const bool idle = node == kStackSentinel;
+        if (idle && has_ray) {
+            io.store(ri, hit, occluded);
+            has_ray = false;
+        }
+        const uint32_t idle_mask = __ballot_sync(kFullMask, idle);
+        const uint32_t chunk_first = ((seq / kRayChunk) * n_warps + warp) * kRayChunk;
+        const bool exhausted = chunk_first >= n_rays;   // chunks only grow: nothing left for this warp
+        if (exhausted && idle_mask == kFullMask) break;
+        if (!exhausted && (int)__popc(idle_mask) >= kRefill) {
+            if (idle) {
+                const uint32_t q = seq + (uint32_t)__popc(idle_mask & lanes_lt);
+                const uint32_t i = ((q / kRayChunk) * n_warps + warp) * kRayChunk + (q % kRayChunk);
+                float3 o, d;
+                float tmax;
+                if (i < n_rays && n_nodes > 0 && io.load(i, o, d, tmax)) {
+                    r = ray_setup(o, d);
+                    ri = i;
+                    has_ray = true;
+                    occluded = false;
+                    tmax_d = (double)tmax;
+                    best_t = tmax_d;
+                    best32 = tmax;
+                    best_prim = 0xFFFFFFFFu;
+                    hit.tri = kHitMiss;
+                    hit.t = hit.u = hit.v = 0.0f;
+                    sp = 0;
+                    stack[sp++] = kStackSentinel;
+                    node = 0;
+                    pend = 0;
+                } else if (i < n_rays) {   // empty scene or empty slot: publish the miss right away
+                    HitRecord miss;
+                    miss.tri = kHitMiss;
+                    miss.t = miss.u = miss.v = 0.0f;
+                    if (n_nodes <= 0) io.store(i, miss, false);
+                }
+            }
+            seq += (uint32_t)__popc(idle_mask);
+            continue;   // re-evaluate: slots without rays leave lanes idle
+        }
+
+        // ---- traverse until enough lanes ran dry -------------------------------
+        do {
+            // all lanes descend; a lane leaves with a second leaf in `node`, or done
+            while (node >= 0 && node != kStackSentinel) {
+                if (STATS) ts.nodes++;
+                const BvhNode2* np = nodes + node;
+                const float4 a = B2PT_LDG4(&np->c0xy);
+                const float4 b = B2PT_LDG4(&np->c1xy);
+                const float4 c = B2PT_LDG4(&np->cz);
+                const float4 m = B2PT_LDG4(&np->child0);
+                float t0, t1;
+                const bool h0 = slab(r, a.x, a.y, a.z, a.w, c.x, c.y, tmin, best32, t0);
+                const bool h1 = slab(r, b.x, b.y, b.z, b.w, c.z, c.w, tmin, best32, t1);
+                const int c0 = (int)f2u_bits(m.x), c1 = (int)f2u_bits(m.y);
+                if (h0 && h1) {
+                    const bool swap = t1 < t0;
+                    node = swap ? c1 : c0;
+                    stack[sp++] = swap ? c0 : c1;
+                } else if (h0) {
+                    node = c0;
+                } else if (h1) {
+                    node = c1;
+                } else {
+                    node = stack[--sp];
+                }
+                if (node < 0 && pend >= 0) {   // postpone the first leaf, keep descending
+                    pend = node;
+                    node = stack[--sp];
+                }
+            }
+            // all lanes test their postponed triangles
+            while (pend < 0) {
+                const int slot = ~pend;
+                pend = 0;
+                if (STATS) ts.tris++;
+                const TriRecord* tp = tris + slot;
+                const float4 ta = B2PT_LDG4(&tp->a);
+                const float4 tb = B2PT_LDG4(&tp->b);
+                const float4 tc = B2PT_LDG4(&tp->c);
+                const float3 v0 = v3(ta.x, ta.y, ta.z), v1 = v3(ta.w, tb.x, tb.y), v2 = v3(tb.z, tb.w, tc.x);
+                if (tri_filter(r.o, r.d, r.d_l1, v0, v1, v2, tmin, best32)) {
+                    if (STATS) ts.exact++;
+                    double t, u, v;
+                    bool bf;
+                    if (tri_exact(r.o, r.d, v0, v1, v2, t, u, v, bf) && t > tmin_d && t < tmax_d) {
+                        if (ANY) {
+                            if (accept((uint32_t)slot, f2u_bits(tc.z), (float)u, (float)v)) {
+                                occluded = true;
+                                node = kStackSentinel;   // done: drop the rest of the stack
+                                break;
+                            }
+                        } else {
+                            const uint32_t prim = f2u_bits(tc.y);
+                            if ((t < best_t || (t == best_t && prim < best_prim)) &&
+                                accept((uint32_t)slot, f2u_bits(tc.z), (float)u, (float)v)) {
+                                best_t = t;
+                                best_prim = prim;
+                                float tf = (float)t;   // round up: the fp32 bound never cuts below best_t
+                                if ((double)tf < t) tf = nextafterf(tf, INFINITY);
+                                best32 = tf;
+                                hit.tri = (uint32_t)slot | (bf ? kHitBackface : 0u);
+                                hit.t = (float)t;
+                                hit.u = (float)u;
+                                hit.v = (float)v;
+                            }
+                        }
+                    }
+                }
+                if (node < 0) {   // the descent stopped on a second leaf: take it next
+                    pend = node;
+                    node = stack[--sp];
+                }
+            }
+        } while ((int)__popc(__ballot_sync(kFullMask, node == kStackSentinel)) < kRefill);
+    }
+}
+
+}  // namespace b2pt
