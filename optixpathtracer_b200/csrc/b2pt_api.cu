@@ -38,7 +38,7 @@ int guarded(B2ptRenderer* r, F&& f) {
 LaunchCfg launch_cfg(B2ptRenderer* r) {
     LaunchCfg lc;
     lc.stream = r->stream;
-    lc.grid = r->sm_count * 8;
+    lc.grid = r->sm_count * trace_grid_blocks_per_sm();
     lc.stats = r->cfg.collect_stats != 0;
     lc.launch_counter = &r->kernel_launches;
     return lc;

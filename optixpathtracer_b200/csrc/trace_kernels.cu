@@ -101,19 +101,18 @@ struct AnyIo {
     }
 };
 
-constexpr int kRefillLanes = 8;
 
-template <bool STATS, bool ALPHA>
-__global__ void __launch_bounds__(kTraceThreads)
+template <bool STATS, bool ALPHA, int MINB = 4>
+__global__ void __launch_bounds__(kTraceThreads, MINB)
 k_closest_p(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active, float tmin, float tmax,
-            HitRecord* __restrict__ hits, TraceCounters* counters) {
+            HitRecord* __restrict__ hits, TraceCounters* counters, WarpPolicy pol) {
     TraceStats ts = {0, 0, 0};
     const ClosestIo io{st, hits, tmax};
     if (ALPHA)
-        trace_persistent<false, STATS, kRefillLanes>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io,
-                                                     AlphaCutout<DeviceTexFetch>{sc, DeviceTexFetch{sc.textures}}, ts);
+        trace_persistent<false, STATS>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io,
+                                                     AlphaCutout<DeviceTexFetch>{sc, DeviceTexFetch{sc.textures}}, ts, pol);
     else
-        trace_persistent<false, STATS, kRefillLanes>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io, AcceptAllHits(), ts);
+        trace_persistent<false, STATS>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io, AcceptAllHits(), ts, pol);
     if (STATS) {
         atomicAdd(&counters->nodes, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris, (unsigned long long)ts.tris);
@@ -121,17 +120,17 @@ k_closest_p(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active,
     }
 }
 
-template <bool STATS, bool ALPHA>
-__global__ void __launch_bounds__(kTraceThreads)
+template <bool STATS, bool ALPHA, int MINB = 4>
+__global__ void __launch_bounds__(kTraceThreads, MINB)
 k_any_p(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, float tmin,
-        uint32_t* __restrict__ info, uint8_t* __restrict__ occluded, TraceCounters* counters) {
+        uint32_t* __restrict__ info, uint8_t* __restrict__ occluded, TraceCounters* counters, WarpPolicy pol) {
     TraceStats ts = {0, 0, 0};
     const AnyIo io{sh, info, occluded};
     if (ALPHA)
-        trace_persistent<true, STATS, kRefillLanes>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io,
-                                                    AlphaCutout<DeviceTexFetch>{sc, DeviceTexFetch{sc.textures}}, ts);
+        trace_persistent<true, STATS>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io,
+                                                    AlphaCutout<DeviceTexFetch>{sc, DeviceTexFetch{sc.textures}}, ts, pol);
     else
-        trace_persistent<true, STATS, kRefillLanes>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io, AcceptAllHits(), ts);
+        trace_persistent<true, STATS>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io, AcceptAllHits(), ts, pol);
     if (STATS) {
         atomicAdd(&counters->nodes_any, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris_any, (unsigned long long)ts.tris);
@@ -140,6 +139,18 @@ k_any_p(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, fl
 }
 
 // B2PT_TRAVERSAL=0 selects the first (thread-per-ray) kernels, for A/B measurements
+int occ_blocks() {
+    static const int v = [] { const char* e = getenv("B2PT_OCC"); return e ? atoi(e) : 8; }();
+    return v;
+}
+WarpPolicy warp_policy() {
+    static const WarpPolicy v = [] {
+        const char* a = getenv("B2PT_REFILL");
+        const char* b = getenv("B2PT_BREAK");
+        return WarpPolicy{a ? atoi(a) : 8, b ? atoi(b) : 16};
+    }();
+    return v;
+}
 bool use_persistent() {
     static const bool v = [] { const char* e = getenv("B2PT_TRAVERSAL"); return !(e && e[0] == '0'); }();
     return v;
@@ -147,19 +158,27 @@ bool use_persistent() {
 
 }  // namespace
 
+int trace_grid_blocks_per_sm() { return occ_blocks() > 0 ? occ_blocks() : 8; }
+
 void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState& st,
                     const uint32_t* n_active, float tmin, float tmax, HitRecord* hits,
                     TraceCounters* counters) {
     const bool alpha = sc.any_alpha_texture != 0;
     if (use_persistent()) {
         if (lc.stats && alpha)
-            k_closest_p<true, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters);
+            k_closest_p<true, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (lc.stats)
-            k_closest_p<true, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters);
+            k_closest_p<true, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (alpha)
-            k_closest_p<false, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters);
+            k_closest_p<false, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (occ_blocks() == 8)
+            k_closest_p<false, false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (occ_blocks() == 6)
+            k_closest_p<false, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (occ_blocks() == 10)
+            k_closest_p<false, false, 10><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else
-            k_closest_p<false, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters);
+            k_closest_p<false, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         if (lc.launch_counter) ++*lc.launch_counter;
         return;
     }
@@ -180,13 +199,19 @@ void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh
     const bool alpha = sc.any_alpha_texture != 0;
     if (use_persistent()) {
         if (lc.stats && alpha)
-            k_any_p<true, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters);
+            k_any_p<true, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (lc.stats)
-            k_any_p<true, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters);
+            k_any_p<true, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (alpha)
-            k_any_p<false, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters);
+            k_any_p<false, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (occ_blocks() == 8)
+            k_any_p<false, false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (occ_blocks() == 6)
+            k_any_p<false, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (occ_blocks() == 10)
+            k_any_p<false, false, 10><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else
-            k_any_p<false, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters);
+            k_any_p<false, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         if (lc.launch_counter) ++*lc.launch_counter;
         return;
     }

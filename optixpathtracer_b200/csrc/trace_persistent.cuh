@@ -29,11 +29,17 @@ constexpr uint32_t kRayChunk = 64;
 
 // Io: bool load(uint32_t i, float3& o, float3& d, float& tmax)   (false: slot carries no ray)
 //     void store(uint32_t i, const HitRecord& h, bool occluded)
-template <bool ANY, bool STATS, int kRefill, class Accept, class Io>
+struct WarpPolicy {
+    int refill_lanes;   // take new rays when this many lanes are idle
+    int break_lanes;    // leave the descent when this many lanes cannot descend (hold two leaves / are done)
+};
+
+template <bool ANY, bool STATS, class Accept, class Io>
 __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ nodes,
                                                  const TriRecord* __restrict__ tris, int n_nodes,
                                                  uint32_t n_rays, float tmin, const Io& io,
-                                                 const Accept& accept, TraceStats& ts) {
+                                                 const Accept& accept, TraceStats& ts, WarpPolicy pol) {
+    const int kRefill = pol.refill_lanes;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t lanes_lt = (1u << lane) - 1u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -103,8 +109,10 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
 
         // ---- traverse until enough lanes ran dry -------------------------------
         do {
-            // all lanes descend; a lane leaves with a second leaf in `node`, or done
-            while (node >= 0 && node != kStackSentinel) {
+            // the warp descends together; a lane stops with a second leaf in `node`, or done, and
+            // the warp leaves the descent once break_lanes lanes have stopped
+            while (true) {
+              if (node >= 0 && node != kStackSentinel) {
                 if (STATS) ts.nodes++;
                 const BvhNode2* np = nodes + node;
                 const float4 a = B2PT_LDG4(&np->c0xy);
@@ -130,6 +138,9 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
                     pend = node;
                     node = stack[--sp];
                 }
+              }
+              const bool stopped = node < 0 || node == kStackSentinel;
+              if ((int)__popc(__ballot_sync(kFullMask, stopped)) >= pol.break_lanes) break;
             }
             // all lanes test their postponed triangles
             while (pend < 0) {

@@ -310,7 +310,7 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
     wc.queued = r->d_counts.get() + 100;
     LaunchCfg lc;
     lc.stream = s;
-    lc.grid = grid;
+    lc.grid = r->sm_count * trace_grid_blocks_per_sm();
     lc.stats = r->cfg.collect_stats != 0;
     lc.launch_counter = &r->kernel_launches;
     auto count = [&](int k = 1) { r->kernel_launches += (uint64_t)k; };

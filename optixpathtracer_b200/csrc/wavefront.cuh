@@ -67,6 +67,9 @@ struct LaunchCfg {
     uint64_t* launch_counter;
 };
 
+// resident traversal blocks per SM the launchers size their grids for (B2PT_OCC overrides)
+int trace_grid_blocks_per_sm();
+
 // K5: closest hit for rays [0, *n_active) of `st`; n_active lives on the device.
 void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState& st,
                     const uint32_t* n_active, float tmin, float tmax, HitRecord* hits,
