@@ -16,7 +16,7 @@ namespace b2pt {
 
 namespace {
 
-constexpr int kTraceThreads = 128;
+constexpr int kTraceThreads = kTraceBlock;
 
 template <bool STATS, bool ALPHA>
 __global__ void __launch_bounds__(kTraceThreads)

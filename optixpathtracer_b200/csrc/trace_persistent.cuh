@@ -26,6 +26,8 @@ namespace b2pt {
 
 constexpr uint32_t kFullMask = 0xffffffffu;
 constexpr uint32_t kRayChunk = 64;
+constexpr int kSharedStack = 16;   // stack levels kept in shared memory
+constexpr int kTraceBlock = 128;   // threads per block of the traversal kernels
 
 // Io: bool load(uint32_t i, float3& o, float3& d, float& tmax)   (false: slot carries no ray)
 //     void store(uint32_t i, const HitRecord& h, bool occluded)
@@ -61,8 +63,14 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
     HitRecord hit;
     hit.tri = kHitMiss;
     hit.t = hit.u = hit.v = 0.0f;
-    int stack[kStackSize];
+    // traversal stack: the first kSharedStack levels live in shared memory ([level][thread]: every
+    // lane has its own bank whatever its depth), deeper levels spill to a local array
+    __shared__ int s_stack[kSharedStack][kTraceBlock];
+    int deep_stack[kStackSize - kSharedStack];
     int sp = 0;
+    const int tid = threadIdx.x;
+#define B2PT_PUSH(v) do { const int v_ = (v); if (sp < kSharedStack) s_stack[sp][tid] = v_; else deep_stack[sp - kSharedStack] = v_; sp++; } while (0)
+#define B2PT_POP() (--sp, sp < kSharedStack ? s_stack[sp][tid] : deep_stack[sp - kSharedStack])
 
     while (true) {
         // ---- finished lanes publish; idle lanes take new rays -----------------
@@ -93,7 +101,7 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
                     hit.tri = kHitMiss;
                     hit.t = hit.u = hit.v = 0.0f;
                     sp = 0;
-                    stack[sp++] = kStackSentinel;
+                    B2PT_PUSH(kStackSentinel);
                     node = 0;
                     pend = 0;
                 } else if (i < n_rays) {   // empty scene or empty slot: publish the miss right away
@@ -126,17 +134,17 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
                 if (h0 && h1) {
                     const bool swap = t1 < t0;
                     node = swap ? c1 : c0;
-                    stack[sp++] = swap ? c0 : c1;
+                    B2PT_PUSH(swap ? c0 : c1);
                 } else if (h0) {
                     node = c0;
                 } else if (h1) {
                     node = c1;
                 } else {
-                    node = stack[--sp];
+                    node = B2PT_POP();
                 }
                 if (node < 0 && pend >= 0) {   // postpone the first leaf, keep descending
                     pend = node;
-                    node = stack[--sp];
+                    node = B2PT_POP();
                 }
               }
               const bool stopped = node < 0 || node == kStackSentinel;
@@ -182,11 +190,14 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
                 }
                 if (node < 0) {   // the descent stopped on a second leaf: take it next
                     pend = node;
-                    node = stack[--sp];
+                    node = B2PT_POP();
                 }
             }
         } while ((int)__popc(__ballot_sync(kFullMask, node == kStackSentinel)) < kRefill);
     }
 }
+
+#undef B2PT_PUSH
+#undef B2PT_POP
 
 }  // namespace b2pt
