@@ -23,6 +23,7 @@
 #include <float.h>
 
 #include "rng.cuh"
+#include "hostmath.cuh"
 
 namespace b2pt {
 
@@ -95,7 +96,7 @@ B2PT_HD float3 ggx_sample_wm(Rng& rng, float3 w, float alpha) {
     rng.next2(ux, uy);
     const float r = sqrtf(ux);
     const float theta = 2.0f * kPi * uy;
-    float px = r * cosf(theta), py = r * sinf(theta);
+    float px = r * hostmath::cosf_host(theta), py = r * hostmath::sinf_host(theta);
     const float h = sqrtf(1.0f - sqr(px));
     const float lerp_t = (1.0f + wh.z) / 2.0f;
     py = (1.0f - lerp_t) * h + lerp_t * py;
@@ -233,8 +234,8 @@ B2PT_HD float3 sample_cosine_hemisphere(Rng& rng) {
             r = oy;
             theta = pi_over_2 - pi_over_4 * (ox / oy);
         }
-        dx = r * cosf(theta);
-        dy = r * sinf(theta);
+        dx = r * hostmath::cosf_host(theta);
+        dy = r * hostmath::sinf_host(theta);
     }
     const float z = sqrtf(fmaxf(0.0f, 1.0f - sqr(dx) - sqr(dy)));
     return v3(dx, dy, z);
@@ -419,7 +420,7 @@ constexpr int kLayerMaxDepth = 10;
 
 B2PT_HD float layer_transmittance(float dz, float3 w) {                 // :97-106
     if (fabsf(dz) <= FLT_MIN) return 1.0f;
-    return expf(-fabsf(dz / w.z));
+    return hostmath::expf_host(-fabsf(dz / w.z));
 }
 B2PT_HD float power_heuristic_1(float fpdf, float gpdf) {               // :91-95, nf = ng = 1
     const float f = 1.0f * fpdf, g = 1.0f * gpdf;

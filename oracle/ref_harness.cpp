@@ -40,6 +40,7 @@ thread_local ShimThreadState g_shim;
 
 #include "../include/b2pt.h"
 #include "host_bvh.h"
+#include "texunit.h"
 
 // The reference declares `extern "C" __constant__ LaunchParams optixLaunchParams`
 // (devicePrograms.cu:42); OptiX fills it per launch.  One copy per thread so
@@ -68,32 +69,15 @@ thread_local uint64_t g_radiance_rays = 0, g_shadow_rays = 0;
 thread_local int g_mode = B2PT_BSDF_AUTO;
 thread_local bool g_force_restated = false;  // AUTO through ref_closesthit_mode (self-check)
 
-inline float4 texel(const ShimTexture& t, int x, int y) {
-    x = ((x % t.width) + t.width) % t.width;
-    y = ((y % t.height) + t.height) % t.height;
-    const unsigned char* p = t.rgba + 4 * ((size_t)y * t.width + x);
-    return make_float4(p[0] / 255.0f, p[1] / 255.0f, p[2] / 255.0f, p[3] / 255.0f);
-}
-
 }  // namespace
 
-// tex2D<float4> of the descriptor in OptixRenderer.cpp:592-603: wrap, bilinear,
-// normalised coordinates, normalised-float reads.  CUDA's linear filter uses
-// 1.8 fixed-point weights (CUDA C Programming Guide, "Linear Filtering").
+// tex2D<float4> of the descriptor in OptixRenderer.cpp:592-603: the texture unit's filter as
+// measured on a B200 (texunit.h).
 float4 shim_tex2d(unsigned long long obj, float x, float y) {
     const ShimTexture& t = *reinterpret_cast<const ShimTexture*>(obj);
-    const float xb = x * (float)t.width - 0.5f, yb = y * (float)t.height - 0.5f;
-    const float fx = floorf(xb), fy = floorf(yb);
-    const float a = floorf((xb - fx) * 256.0f + 0.5f) / 256.0f;
-    const float b = floorf((yb - fy) * 256.0f + 0.5f) / 256.0f;
-    const int i = (int)fx, j = (int)fy;
-    const float4 t00 = texel(t, i, j), t10 = texel(t, i + 1, j), t01 = texel(t, i, j + 1),
-                 t11 = texel(t, i + 1, j + 1);
-    auto mixc = [&](float c00, float c10, float c01, float c11) {
-        return (1 - a) * (1 - b) * c00 + a * (1 - b) * c10 + (1 - a) * b * c01 + a * b * c11;
-    };
-    return make_float4(mixc(t00.x, t10.x, t01.x, t11.x), mixc(t00.y, t10.y, t01.y, t11.y),
-                       mixc(t00.z, t10.z, t01.z, t11.z), mixc(t00.w, t10.w, t01.w, t11.w));
+    float o[4];
+    oracle::texunit_sample(t.rgba, t.width, t.height, x, y, o);
+    return make_float4(o[0], o[1], o[2], o[3]);
 }
 
 static void ref_closesthit_mode();  // below

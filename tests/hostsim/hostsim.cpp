@@ -211,6 +211,14 @@ void hostsim_bsdf_sample(int bsdf, int lcg_mode, int64_t n, const float* albedo,
     }
 }
 
+// kind 0 sin, 1 cos, 2 exp: hostmath.cuh's restatement beside this host's libm
+void hostsim_hostmath(int kind, int64_t n, const float* x, float* restated, float* libm) {
+    for (int64_t i = 0; i < n; i++) {
+        restated[i] = kind == 0 ? hostmath::sinf_host(x[i]) : kind == 1 ? hostmath::cosf_host(x[i]) : hostmath::expf_host(x[i]);
+        libm[i] = kind == 0 ? ::sinf(x[i]) : kind == 1 ? ::cosf(x[i]) : ::expf(x[i]);
+    }
+}
+
 void hostsim_bsdf_pdf(int bsdf, int64_t n, const float* roughness, const float* wo, const float* wi,
                       int reflection, int transmission, float* pdf_out) {
     for (int64_t i = 0; i < n; i++)
@@ -221,29 +229,17 @@ void hostsim_bsdf_pdf(int bsdf, int64_t n, const float* roughness, const float* 
 
 // ---- whole frames: the wavefront stages (integrator.cuh) run per pixel --------
 #include "../../optixpathtracer_b200/csrc/alpha.cuh"
+#include "../../oracle/texunit.h"
 
 namespace {
 
-struct HostTexFetch {   // same filter as oracle/ref_harness.cpp::shim_tex2d
+struct HostTexFetch {   // the texture unit as measured (oracle/texunit.h), as in oracle/ref_harness.cpp
     const B2ptTexture* tex;
-    static float4 texel(const B2ptTexture& t, int x, int y) {
-        x = ((x % t.width) + t.width) % t.width;
-        y = ((y % t.height) + t.height) % t.height;
-        const uint8_t* p = t.rgba + 4 * ((size_t)y * t.width + x);
-        return make_float4(p[0] / 255.0f, p[1] / 255.0f, p[2] / 255.0f, p[3] / 255.0f);
-    }
     float4 operator()(int id, float x, float y) const {
         const B2ptTexture& t = tex[id];
-        const float xb = x * (float)t.width - 0.5f, yb = y * (float)t.height - 0.5f;
-        const float fx = floorf(xb), fy = floorf(yb);
-        const float a = floorf((xb - fx) * 256.0f + 0.5f) / 256.0f, b = floorf((yb - fy) * 256.0f + 0.5f) / 256.0f;
-        const int i = (int)fx, j = (int)fy;
-        const float4 t00 = texel(t, i, j), t10 = texel(t, i + 1, j), t01 = texel(t, i, j + 1), t11 = texel(t, i + 1, j + 1);
-        auto mixc = [&](float c00, float c10, float c01, float c11) {
-            return (1 - a) * (1 - b) * c00 + a * (1 - b) * c10 + (1 - a) * b * c01 + a * b * c11;
-        };
-        return make_float4(mixc(t00.x, t10.x, t01.x, t11.x), mixc(t00.y, t10.y, t01.y, t11.y),
-                           mixc(t00.z, t10.z, t01.z, t11.z), mixc(t00.w, t10.w, t01.w, t11.w));
+        float o[4];
+        oracle::texunit_sample(t.rgba, t.width, t.height, x, y, o);
+        return make_float4(o[0], o[1], o[2], o[3]);
     }
 };
 

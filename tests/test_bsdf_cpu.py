@@ -14,7 +14,7 @@ import numpy as np
 import pytest
 
 from tests import cases
-from tests.util import RefOracle, bits
+from tests.util import HostSim, RefOracle, bits
 
 GOLD = Path(__file__).resolve().parent / "golden"
 f32 = np.float32
@@ -120,3 +120,21 @@ def test_philox_is_counter_based(hostsim):
     b, _ = hostsim.render(sc, 32, 18, bsdf_mode=0, rng_mode=0, max_bounces=4, frame_first=2, n_frames=1)
     c, _ = hostsim.render(sc, 32, 18, bsdf_mode=0, rng_mode=0, seed=99, max_bounces=4, frame_first=2, n_frames=1)
     assert _same(a[1], b[0]) and not _same(b[0], c[0])
+
+
+def test_hostmath_is_the_host_library():
+    hs = HostSim()
+    """hostmath.cuh (the sin/cos/exp the shading kernels use) against this host's libm, bit for bit."""
+    import ctypes as C
+    rng = np.random.default_rng(11)
+    sweeps = {
+        0: np.concatenate([rng.uniform(-0.2, 6.5, 400000), rng.uniform(-119, 119, 100000), [0.0, 1e-5, 0.785398, 3.14159274]]),
+        1: np.concatenate([rng.uniform(-0.2, 6.5, 400000), rng.uniform(-119, 119, 100000), [0.0, 1e-5, 0.785398, 3.14159274]]),
+        2: np.concatenate([-rng.uniform(0, 40, 400000), rng.uniform(-110, 90, 100000), [0.0, -np.inf, np.inf, -1e-30, -103.9, -104.1]]),
+    }
+    for kind, x in sweeps.items():
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        a, b = np.empty_like(x), np.empty_like(x)
+        hs.lib.hostsim_hostmath(C.c_int(kind), C.c_int64(len(x)), x.ctypes.data_as(C.c_void_p),
+                                a.ctypes.data_as(C.c_void_p), b.ctypes.data_as(C.c_void_p))
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32)), f"kind {kind}: {(a.view(np.uint32) != b.view(np.uint32)).sum()} differ"
