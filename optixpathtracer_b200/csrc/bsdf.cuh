@@ -427,17 +427,20 @@ B2PT_HD float power_heuristic_1(float fpdf, float gpdf) {               // :91-9
     return sqr(f) / (sqr(f) + sqr(g));
 }
 
-// the two interfaces behind one switch (Layer_f / Layer_Sample_f / Layer_PDF, :110-135)
-B2PT_HD float3 interface_f(bool top, const ShadePoint& sp, float3 wo, float3 wi, bool radiance) {
+// the two interfaces behind one switch (Layer_f / Layer_Sample_f / Layer_PDF, :110-135).
+// Kept as real calls on the device: the walks below reach them from a dozen places, and inlined the
+// layered kernel was 18 000 instructions (290 KB) whose warps stalled on instruction fetch 70 % of
+// the time (profiles/r01_k_shade_layered_*.csv).
+B2PT_HD_CALL float3 interface_f(bool top, const ShadePoint& sp, float3 wo, float3 wi, bool radiance) {
     return top ? dielectric_f(sp, wo, wi, radiance) : diffuse_f(sp, wo, wi);
 }
 template <class Rng>
-B2PT_HD bool interface_sample(bool top, Rng& rng, const ShadePoint& sp, float3 wo, bool radiance,
+B2PT_HD_CALL bool interface_sample(bool top, Rng& rng, const ShadePoint& sp, float3 wo, bool radiance,
                               bool reflection, bool transmission, BsdfSample& s) {
     return top ? dielectric_sample(rng, sp, wo, radiance, reflection, transmission, s)
                : diffuse_sample(rng, sp, wo, reflection, s);
 }
-B2PT_HD float interface_pdf(bool top, const ShadePoint& sp, float3 wo, float3 wi, bool reflection,
+B2PT_HD_CALL float interface_pdf(bool top, const ShadePoint& sp, float3 wo, float3 wi, bool reflection,
                             bool transmission) {
     return top ? dielectric_pdf(sp, wo, wi, reflection, transmission) : diffuse_pdf(wo, wi, reflection);
 }

@@ -14,7 +14,9 @@
 #if defined(__CUDACC__)
 #define B2PT_HD __host__ __device__ __forceinline__
 #define B2PT_D __device__ __forceinline__
+#define B2PT_HD_CALL __host__ __device__ __noinline__ inline   // a real call (code size over call overhead)
 #else
+#define B2PT_HD_CALL inline
 #define B2PT_HD inline
 #define B2PT_D inline
 #endif
