@@ -172,7 +172,7 @@ def run_reference(args, cfg):
             "cpu_baseline": {"value": msps, "unit": "Msamples/s", "cores": cores, "kind": "reference", "sample": desc,
                              "mrays_per_s": mrays},
             "e2e": {"value": msps, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 def algorithmic_bytes_per_ray(scene, w, h, depth, mode, spp=1):
@@ -363,13 +363,34 @@ def run_b2pt(args, cfg):
             "image_mean": float(mean_img.mean()), "image_finite": bool(np.isfinite(mean_img).all()),
             "nan_samples": st["nan_pixels"],
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}
-    print(json.dumps(line))
+    emit(line)
     r.close()
     if world > 1:
         dist.destroy_process_group()
 
 
+_JSON_OUT = None
+
+
+def guard_stdout():
+    """stdout carries exactly one JSON line.  The reference's device code prints from a debug pixel
+    ((760, 369) at frame.id 10: devicePrograms.cu:639-643, PBRT/Conductor.h:143-172) and that printf runs
+    in this process when the host-compiled reference is timed, so fd 1 is pointed at stderr and the JSON
+    line goes out through a private duplicate of the real stdout."""
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line):
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    guard_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=16)
