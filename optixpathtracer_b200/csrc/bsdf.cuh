@@ -61,7 +61,7 @@ B2PT_HD float sin_phi(float3 w) {
 }
 
 // ---- Trowbridge-Reitz microfacet model (Microfacet.h) ---------------------
-B2PT_HD float ggx_d(float3 wm, float alpha) {                       // :9-20
+B2PT_HD_CALL float ggx_d(float3 wm, float alpha) {                       // :9-20
     const float t2 = tan2_theta(wm);
     if (isinf(t2)) return 0.0f;
     const float c4 = sqr(cos2_theta(wm));
@@ -69,7 +69,7 @@ B2PT_HD float ggx_d(float3 wm, float alpha) {                       // :9-20
     const float e = t2 * (sqr(cos_phi(wm) / alpha) + sqr(sin_phi(wm) / alpha));
     return 1.0f / (kPi * alpha * alpha * c4 * sqr(1.0f + e));
 }
-B2PT_HD float ggx_lambda(float3 w, float alpha) {                   // :46-52
+B2PT_HD_CALL float ggx_lambda(float3 w, float alpha) {                   // :46-52
     const float t2 = tan2_theta(w);
     if (isinf(t2)) return 0.0f;
     const float a2 = sqr(cos_phi(w) * alpha) + sqr(sin_phi(w) * alpha);
@@ -86,14 +86,14 @@ B2PT_HD float ggx_visible_pdf(float3 w, float3 wm, float alpha) {
 
 // Heitz visible-normal sampling (:90-121); two draws, taken as the pair
 // `glm::vec2(rnd, rnd)` of SampleUniformDiskPolar (random.h:76-84).
-template <class Rng>
-B2PT_HD float3 ggx_sample_wm(Rng& rng, float3 w, float alpha) {
+// The body is a real call on the device (B2PT_HD_CALL): the GGX helpers are reached from many places
+// of the dielectric / layered code and, inlined everywhere, made kernels of 7 000 - 18 000 instructions
+// that stalled on instruction fetch.
+B2PT_HD_CALL float3 ggx_sample_wm_u(float3 w, float alpha, float ux, float uy) {
     float3 wh = normalize(v3(alpha * w.x, alpha * w.y, w.z));
     if (wh.z < 0.0f) wh = -wh;
     const float3 t1 = wh.z < 0.99999f ? normalize(cross(v3(0.0f, 0.0f, 1.0f), wh)) : v3(1.0f, 0.0f, 0.0f);
     const float3 t2 = cross(wh, t1);
-    float ux, uy;
-    rng.next2(ux, uy);
     const float r = sqrtf(ux);
     const float theta = 2.0f * kPi * uy;
     float px = r * hostmath::cosf_host(theta), py = r * hostmath::sinf_host(theta);
@@ -104,10 +104,16 @@ B2PT_HD float3 ggx_sample_wm(Rng& rng, float3 w, float alpha) {
     const float3 nh = px * t1 + py * t2 + pz * wh;
     return normalize(v3(alpha * nh.x, alpha * nh.y, fmaxf(1e-6f, nh.z)));
 }
+template <class Rng>
+B2PT_HD float3 ggx_sample_wm(Rng& rng, float3 w, float alpha) {
+    float ux, uy;
+    rng.next2(ux, uy);
+    return ggx_sample_wm_u(w, alpha, ux, uy);
+}
 
 // ---- Fresnel ---------------------------------------------------------------
 // unpolarised dielectric Fresnel (Dielectric.h:20-44)
-B2PT_HD float fresnel_dielectric(float cos_i, float ior) {
+B2PT_HD_CALL float fresnel_dielectric(float cos_i, float ior) {
     cos_i = clampf(cos_i, -1.0f, 1.0f);
     if (cos_i < 0.0f) {
         ior = 1.0f / ior;
@@ -284,7 +290,7 @@ B2PT_HD bool refract(float3 wi, float3 n, float eta, float& etap, float3& wt) {
 }
 
 // generalised half vector, oriented to +z: glm::faceforward(-n, (0,0,1), n)
-B2PT_HD float3 half_vector_up(float3 wm) {
+B2PT_HD_CALL float3 half_vector_up(float3 wm) {
     const float3 n = normalize(wm);
     return n.z < 0.0f ? -n : n;
 }
@@ -418,7 +424,7 @@ constexpr float kLayerThickness = 0.01f;
 constexpr int kLayerWalks = 5;       // nSamples
 constexpr int kLayerMaxDepth = 10;
 
-B2PT_HD float layer_transmittance(float dz, float3 w) {                 // :97-106
+B2PT_HD_CALL float layer_transmittance(float dz, float3 w) {                 // :97-106
     if (fabsf(dz) <= FLT_MIN) return 1.0f;
     return hostmath::expf_host(-fabsf(dz / w.z));
 }

@@ -97,6 +97,13 @@ B2PT_HD void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
+// one 4-draw block; a real call on the device (ten rounds x every draw site is a lot of code)
+B2PT_HD_CALL uint4 philox_block(uint32_t block, uint32_t c1, uint32_t c2, uint32_t k0, uint32_t k1) {
+    uint32_t o[4];
+    philox4x32_10(block, c1, c2, 0x62327074u /* "b2pt" */, k0, k1, o);
+    return make_uint4(o[0], o[1], o[2], o[3]);
+}
+
 struct PhiloxRng {
     uint32_t k0, k1;      // key: seed ^ pixel, seed_hi ^ sample index
     uint32_t c1, c2;      // counter words: (bounce | stage << 16), stream id
@@ -113,7 +120,8 @@ struct PhiloxRng {
 
     B2PT_HD uint32_t next_u32() {
         if (have == 0) {
-            philox4x32_10(block++, c1, c2, 0x62327074u /* "b2pt" */, k0, k1, buf);
+            const uint4 o = philox_block(block++, c1, c2, k0, k1);
+            buf[0] = o.x; buf[1] = o.y; buf[2] = o.z; buf[3] = o.w;
             have = 4;
         }
         // select without dynamic indexing (keeps buf in registers)

@@ -1,7 +1,7 @@
 #!/bin/bash
 # A/B helper (run under gpurun): tools/ab.sh "ENV=.. ENV2=.." ...   one bench run per argument
 for v in "$@"; do
-  env $v python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/ab.json 2>gpurun_out/ab.err || tail -3 gpurun_out/ab.err
+  env $v python bench.py ${AB_ARGS:---steps 4 --warmup 3} --no-cpu-baseline > gpurun_out/ab.json 2>gpurun_out/ab.err || tail -3 gpurun_out/ab.err
   python - "$v" <<'PY'
 import json,sys
 d=json.load(open("gpurun_out/ab.json")); r=d["roofline"]
