@@ -428,6 +428,9 @@ B2PT_HD_CALL float layer_transmittance(float dz, float3 w) {                 // 
     if (fabsf(dz) <= FLT_MIN) return 1.0f;
     return hostmath::expf_host(-fabsf(dz / w.z));
 }
+// float3 / float as a real call on the device: the walks divide by a pdf in a dozen places and each
+// inline IEEE division is ~12 instructions x 3 components
+B2PT_HD_CALL float3 div3(float3 a, float s) { return a / s; }
 B2PT_HD float power_heuristic_1(float fpdf, float gpdf) {               // :91-95, nf = ng = 1
     const float f = 1.0f * fpdf, g = 1.0f * gpdf;
     return sqr(f) / (sqr(f) + sqr(g));
@@ -485,14 +488,14 @@ B2PT_HD float3 layered_f(Rng& rng, const ShadePoint& sp, float3 wo, float3 wi) {
         const bool wis_ok = interface_sample(exit_top, rng, sp, wi, false, false, true, wis);
         if (!usable(wis_ok, wis)) continue;
 
-        float3 beta = wos.f * fabsf(wos.wi.z) / wos.pdf;
+        float3 beta = div3(wos.f * fabsf(wos.wi.z), wos.pdf);
         float z = thickness;
         float3 w = wos.wi;
         for (int depth = 0; depth < kLayerMaxDepth; ++depth) {
             if (depth > 3 && max3(beta) < 0.25f) {
                 const float q = fmaxf(0.0f, 1.0f - max3(beta));
                 if (rr.next() < q) break;
-                beta /= 1.0f - q;
+                beta = div3(beta, 1.0f - q);
             }
             z = (z == thickness) ? 0.0f : thickness;
             beta *= layer_transmittance(thickness, w);
@@ -500,20 +503,20 @@ B2PT_HD float3 layered_f(Rng& rng, const ShadePoint& sp, float3 wo, float3 wi) {
                 BsdfSample bs;
                 const bool ok = interface_sample(exit_top, rng, sp, -w, true, true, false, bs);
                 if (!usable(ok, bs)) break;
-                beta *= bs.f * fabsf(bs.wi.z) / bs.pdf;
+                beta *= div3(bs.f * fabsf(bs.wi.z), bs.pdf);
                 w = bs.wi;
             } else {
                 if (!nonexit_specular) {  // NEE along the presampled wis
                     float wt = 1.0f;
                     if (!exit_specular)
                         wt = power_heuristic_1(wis.pdf, interface_pdf(nonexit_top, sp, -w, -wis.wi, true, true));
-                    f += beta * interface_f(nonexit_top, sp, -w, -wis.wi, true) * fabsf(wis.wi.z) * wt *
-                         layer_transmittance(thickness, wis.wi) * wis.f / wis.pdf;
+                    f += div3(beta * interface_f(nonexit_top, sp, -w, -wis.wi, true) * fabsf(wis.wi.z) * wt *
+                                  layer_transmittance(thickness, wis.wi) * wis.f, wis.pdf);
                 }
                 BsdfSample bs;
                 const bool ok = interface_sample(nonexit_top, rng, sp, -w, true, true, false, bs);
                 if (!usable(ok, bs)) break;
-                beta *= bs.f * fabsf(bs.wi.z) / bs.pdf;
+                beta *= div3(bs.f * fabsf(bs.wi.z), bs.pdf);
                 w = bs.wi;
                 if (!exit_specular) {  // NEE along the sampled direction
                     const float3 f_exit = interface_f(exit_top, sp, -w, wi, true);

@@ -21,6 +21,7 @@
 // where a path sits in the buffers (atomics order) never enters the result, and
 // K9 adds the samples of a pixel in sample order.  Same inputs => same bits.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "render.h"
@@ -147,8 +148,8 @@ k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restri
 
 // ---- K7a-d -------------------------------------------------------------------
 // One launch per BSDF: every thread of the kernel runs the same BSDF code.
-template <int KIND, class Rng>
-__global__ void __launch_bounds__(kThreads)
+template <int KIND, class Rng, int MINB = 6>
+__global__ void __launch_bounds__(kThreads, MINB)
 k_shade(WaveParams wp, PathState st, PathState nx, SurfaceState sf, const uint32_t* __restrict__ queue,
         WaveCounts wc, uint32_t bounce, float* __restrict__ wave_out) {
     const uint32_t n = wc.queued[4 * bounce + KIND];
@@ -353,7 +354,20 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
         if (kinds[0]) { k_shade<kBsdfConductor, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 0 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
         if (kinds[1]) { k_shade<kBsdfDiffuse, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 1 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
         if (kinds[2]) { k_shade<kBsdfDielectric, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 2 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
-        if (kinds[3]) { k_shade<kBsdfLayered, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+        if (kinds[3]) {
+            // the layered kernel waits on instruction fetch (4 500 instructions, twice the instruction cache):
+            // more resident warps hide it better than more registers per thread help (A/B: B2PT_SHADE_OCC)
+            static const int occ = [] { const char* e = getenv("B2PT_SHADE_OCC"); return e ? atoi(e) : 8; }();
+            const int g = r->sm_count * std::max(occ, 4) * 2;
+            if (occ >= 8)
+                k_shade<kBsdfLayered, Rng, 8><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
+            else if (occ >= 6)
+                k_shade<kBsdfLayered, Rng, 6><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
+            else
+                k_shade<kBsdfLayered, Rng, 4><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
+            count();
+            mark(kClsShade);
+        }
     }
     k_accumulate<<<r->sm_count * 4, 256, 0, s>>>(wp, r->d_wave_out.get(), dst, overwrite ? 1 : 0, r->d_counters.get());
     k_tally<<<1, 32, 0, s>>>(wc, wp.max_bounces, wp.n_lights > 0 ? 1 : 0, r->d_counters.get());
