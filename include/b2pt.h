@@ -211,6 +211,20 @@ int b2pt_get_accumulation_device(B2ptRenderer* r, float** d_rgb_sum, uint32_t* s
 int b2pt_download_accumulation(B2ptRenderer* r, float* h_rgb_sum, uint32_t* spp_accumulated);
 int b2pt_upload_accumulation(B2ptRenderer* r, const float* h_rgb_sum, uint32_t spp_accumulated);
 
+/* ---- image output (replaces the GL display pass and WriteImage.cpp) ----
+ * All of them act on the running mean sum/spp of the accumulation buffer.
+ * b2pt_display_rgb8: Final.frag:12-36 (LinearToSRGB8 when apply_oetf != 0) then
+ *   WriteImage.cpp:16-18 (clamp to [0,1], (uint8_t)(c * 255.0f)); h_rgb8 holds W*H*3
+ *   bytes; top_row_first != 0 flips the rows (files), 0 keeps the API's row 0 = bottom.
+ * b2pt_write_bmp / b2pt_write_png: the same 8-bit image as a file (WriteBMP :9-33;
+ *   PNG: what the README's Images/PNGs hold).
+ * b2pt_write_exr: WriteEXR :36-99 — FLOAT channels B, G, R, top row first, a pixel
+ *   with a NaN component written as 0; scan-line OpenEXR without compression.    */
+int b2pt_display_rgb8(B2ptRenderer* r, int32_t apply_oetf, int32_t top_row_first, uint8_t* h_rgb8);
+int b2pt_write_bmp(B2ptRenderer* r, const char* path, int32_t apply_oetf);
+int b2pt_write_png(B2ptRenderer* r, const char* path, int32_t apply_oetf);
+int b2pt_write_exr(B2ptRenderer* r, const char* path);
+
 /* Record a CUDA event after every kernel of the render calls and attribute the
  * elapsed device time per kernel class (B2ptStats.device_ms_kernel).         */
 int b2pt_set_kernel_timing(B2ptRenderer* r, int32_t on);

@@ -12,4 +12,7 @@ def __getattr__(name):
     if name == "OptixRenderer":
         from .api import OptixRenderer
         return OptixRenderer
+    if name == "OptixView":
+        from .view import OptixView
+        return OptixView
     raise AttributeError(name)

@@ -90,6 +90,10 @@ SIGNATURES = {
     "b2pt_clear_accumulation": (C.c_int, [_H]),
     "b2pt_get_accumulation_device": (C.c_int, [_H, C.POINTER(C.c_void_p), c_uint32_p]),
     "b2pt_download_accumulation": (C.c_int, [_H, c_float_p, c_uint32_p]),
+    "b2pt_display_rgb8": (C.c_int, [_H, C.c_int32, C.c_int32, C.POINTER(C.c_uint8)]),
+    "b2pt_write_bmp": (C.c_int, [_H, C.c_char_p, C.c_int32]),
+    "b2pt_write_png": (C.c_int, [_H, C.c_char_p, C.c_int32]),
+    "b2pt_write_exr": (C.c_int, [_H, C.c_char_p]),
     "b2pt_upload_accumulation": (C.c_int, [_H, c_float_p, C.c_uint32]),
     "b2pt_set_kernel_timing": (C.c_int, [_H, C.c_int32]),
     "b2pt_get_stats": (C.c_int, [_H, C.POINTER(B2ptStats)]),

@@ -196,6 +196,24 @@ class OptixRenderer:
         a = np.ascontiguousarray(rgb_sum, dtype=f32)
         check(self._h, self.lib.b2pt_upload_accumulation(self._h, _fp(a), int(spp)))
 
+    # -- image output (Final.frag display transform, WriteImage.cpp) -----------------
+    def Display(self, apply_oetf: bool = True, top_row_first: bool = True) -> np.ndarray:
+        """8-bit image of the running mean: (H, W, 3) uint8."""
+        out = np.empty((self.height, self.width, 3), dtype=np.uint8)
+        check(self._h, self.lib.b2pt_display_rgb8(self._h, int(apply_oetf), int(top_row_first),
+                                                  out.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return out
+
+    def WriteBMP(self, path, apply_oetf: bool = False):
+        """WriteImage::WriteBMP (the reference writes the linear pixels, clamped: apply_oetf False)."""
+        check(self._h, self.lib.b2pt_write_bmp(self._h, str(path).encode(), int(apply_oetf)))
+
+    def WritePNG(self, path, apply_oetf: bool = True):
+        check(self._h, self.lib.b2pt_write_png(self._h, str(path).encode(), int(apply_oetf)))
+
+    def WriteEXR(self, path):
+        check(self._h, self.lib.b2pt_write_exr(self._h, str(path).encode()))
+
     def Stats(self) -> dict:
         s = B2ptStats()
         check(self._h, self.lib.b2pt_get_stats(self._h, C.byref(s)))

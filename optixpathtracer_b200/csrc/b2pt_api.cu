@@ -263,6 +263,25 @@ int b2pt_upload_accumulation(B2ptRenderer* r, const float* h_rgb_sum, uint32_t s
     });
 }
 
+// ---- image output ----------------------------------------------------------
+
+int b2pt_display_rgb8(B2ptRenderer* r, int32_t apply_oetf, int32_t top_row_first, uint8_t* h_rgb8) {
+    if (!r || !h_rgb8) return B2PT_E_INVALID;
+    return guarded(r, [&] { display_to_host(r, apply_oetf != 0, top_row_first != 0, h_rgb8); });
+}
+int b2pt_write_bmp(B2ptRenderer* r, const char* path, int32_t apply_oetf) {
+    if (!r || !path) return B2PT_E_INVALID;
+    return guarded(r, [&] { write_bmp(r, path, apply_oetf != 0); });
+}
+int b2pt_write_png(B2ptRenderer* r, const char* path, int32_t apply_oetf) {
+    if (!r || !path) return B2PT_E_INVALID;
+    return guarded(r, [&] { write_png(r, path, apply_oetf != 0); });
+}
+int b2pt_write_exr(B2ptRenderer* r, const char* path) {
+    if (!r || !path) return B2PT_E_INVALID;
+    return guarded(r, [&] { write_exr(r, path); });
+}
+
 // ---- statistics ------------------------------------------------------------
 
 int b2pt_get_stats(const B2ptRenderer* rc, B2ptStats* out) {
