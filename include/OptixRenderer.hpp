@@ -94,6 +94,12 @@ class OptixRendererT {
     void SetRng(int mode, uint64_t seed) { check(r_, b2pt_set_rng(r_, mode, seed)); }
     template <class Vec3>
     void RenderAccumulate(int spp, Vec3 h_mean[]) { check(r_, b2pt_render_accumulate(r_, spp, reinterpret_cast<float*>(h_mean))); }
+    void ClearAccumulation() { check(r_, b2pt_clear_accumulation(r_)); }
+    // WriteImage::WriteEXR / WriteBMP (Renderer/Images/WriteImage.cpp:9-99) and the Final.frag display
+    // transform, applied to the accumulated image without leaving the library
+    void WriteEXR(const char* path) { check(r_, b2pt_write_exr(r_, path)); }
+    void WriteBMP(const char* path, bool apply_oetf = false) { check(r_, b2pt_write_bmp(r_, path, apply_oetf ? 1 : 0)); }
+    void WritePNG(const char* path, bool apply_oetf = true) { check(r_, b2pt_write_png(r_, path, apply_oetf ? 1 : 0)); }
     B2ptRenderer* handle() const { return r_; }
 
   private:
