@@ -184,13 +184,14 @@ def algorithmic_bytes_per_ray(scene, w, h, depth, mode, spp=1):
         r.Resize((w, h)); r.SetCamera(scene["camera"]); r.SetLights(scene["lights"])
         r.RenderAccumulate(spp, download=False)
         st = r.Stats()
-    rr, sr = max(st["radiance_rays"], 1), max(st["shadow_rays"], 1)
+    rr, sr = max(st["radiance_rays"], 1), max(st["shadow_rays_traced"], 1)   # per ray actually traced
     b_closest = (st["nodes_visited"] * st["node_bytes"] + st["triangles_tested"] * st["triangle_bytes"]) / rr + 48.0
     b_any = (st["nodes_visited_shadow"] * st["node_bytes"] + st["triangles_tested_shadow"] * st["triangle_bytes"]) / sr + 36.0
     return {"closest": b_closest, "any": b_any, "nodes_per_ray": st["nodes_visited"] / rr,
             "tris_per_ray": st["triangles_tested"] / rr, "exact_per_ray": st["exact_tests"] / rr,
             "nodes_per_shadow_ray": st["nodes_visited_shadow"] / sr, "tris_per_shadow_ray": st["triangles_tested_shadow"] / sr,
-            "rays_per_sample": (st["radiance_rays"] + st["shadow_rays"]) / max(st["samples"], 1)}
+            "rays_per_sample": (st["radiance_rays"] + st["shadow_rays_traced"]) / max(st["samples"], 1),
+            "shadow_rays_culled_frac": 1.0 - st["shadow_rays_traced"] / max(st["shadow_rays"], 1)}
 
 
 class DevicePtr:
@@ -265,7 +266,7 @@ def run_b2pt(args, cfg):
     st = r.Stats()
     r.SetKernelTiming(False)
     t = torch.tensor([dev_ms, st["device_ms_render"], wall_s * 1e3], device=f"cuda:{local}", dtype=torch.float64)
-    rays = torch.tensor([st["radiance_rays"], st["shadow_rays"], st["kernel_launches"]], device=f"cuda:{local}", dtype=torch.float64)
+    rays = torch.tensor([st["radiance_rays"], st["shadow_rays_traced"], st["kernel_launches"]], device=f"cuda:{local}", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(rays, op=dist.ReduceOp.SUM)
@@ -332,7 +333,7 @@ def run_b2pt(args, cfg):
                 "ms_per_launch": closest_ms / max(n_k[0], 1), "launches": n_k[0],
                 "share_of_step": {"closest": ms_k[0] / render_ms, "any": ms_k[1] / render_ms, "surface": ms_k[2] / render_ms,
                                   "shade": ms_k[3] / render_ms, "other": ms_k[4] / render_ms},
-                "shadow": {"achieved": st["shadow_rays"] * bpr["any"] / (max(ms_k[1], 1e-9) * 1e-3) / 1e9,
+                "shadow": {"achieved": st["shadow_rays_traced"] * bpr["any"] / (max(ms_k[1], 1e-9) * 1e-3) / 1e9,
                            "bytes_per_ray": bpr["any"]},
                 "note": "scene BVH+triangles are L2-resident for the README scenes (16 MB < 126 MB L2): the HBM fraction can "
                         "exceed what DRAM traffic shows; see DESIGN.md"}
@@ -358,7 +359,8 @@ def run_b2pt(args, cfg):
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(rays[2].item()),
             "mrays_per_s": float(rays[0].item() + rays[1].item()) / (dev_ms * 1e-3) / 1e6,
-            "rays_per_sample": bpr["rays_per_sample"],
+            "rays_per_sample": bpr["rays_per_sample"],   # rays really traced (K5 + K8)
+            "shadow_rays_culled_frac": bpr["shadow_rays_culled_frac"],
             "device_ms_render_max": render_ms, "wall_ms": wall_ms,
             "image_mean": float(mean_img.mean()), "image_finite": bool(np.isfinite(mean_img).all()),
             "nan_samples": st["nan_pixels"],

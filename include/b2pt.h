@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B2PT_ABI_VERSION 2
+#define B2PT_ABI_VERSION 3
 
 /* ---- status codes ------------------------------------------------------ */
 enum {
@@ -152,6 +152,11 @@ typedef struct B2ptStats {
      * [3] K7 shade (all BSDFs), [4] K4 raygen + K9 accumulate + bookkeeping   */
     double   device_ms_kernel[5];
     uint64_t launches_kernel[5];
+    /* shadow rays K8 really traced.  shadow_rays above is the reference's count (one per
+     * shaded hit while lights exist); the difference are rays whose BSDF value towards the
+     * light is exactly zero (mirror / smooth glass, light behind an opaque surface) and which
+     * K6 therefore never emits — same image, fewer rays.             */
+    uint64_t shadow_rays_traced;
 } B2ptStats;
 
 typedef struct B2ptRenderer B2ptRenderer;

@@ -65,7 +65,8 @@ class B2ptStats(C.Structure):
                 ("scene_device_bytes", C.c_int64),
                 ("nodes_visited_shadow", C.c_uint64), ("triangles_tested_shadow", C.c_uint64),
                 ("exact_tests_shadow", C.c_uint64),
-                ("device_ms_kernel", C.c_double * 5), ("launches_kernel", C.c_uint64 * 5)]
+                ("device_ms_kernel", C.c_double * 5), ("launches_kernel", C.c_uint64 * 5),
+                ("shadow_rays_traced", C.c_uint64)]
 
 
 # name -> (restype, argtypes); exactly the symbols include/b2pt.h declares.

@@ -314,6 +314,7 @@ int b2pt_get_stats(const B2ptRenderer* rc, B2ptStats* out) {
             out->device_ms_kernel[k] = r->ms_kernel[k];
             out->launches_kernel[k] = r->launches_kernel_cls[k];
         }
+        out->shadow_rays_traced = out->shadow_rays - c.shadow_culled;
     });
 }
 

@@ -44,6 +44,7 @@ struct WaveParams {
     uint32_t spw;          // samples in this wave
     uint32_t frame0;       // frame.id of the wave's first sample
     uint32_t capacity;     // slots per SoA array
+    int32_t cull_nee;      // 1: K6 drops shadow rays with a provably zero contribution (B2PT_CULL_NEE=0 disables)
 };
 
 // counters of one wave, zeroed before K4:  active[b] = rays traced at bounce b,
@@ -96,8 +97,10 @@ __device__ __forceinline__ uint32_t warp_append(bool want, uint32_t* counter) {
 template <class Rng>
 __global__ void __launch_bounds__(kThreads)
 k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restrict__ hits, SurfaceState sf,
-          ShadowRays sh, uint32_t* __restrict__ queues, WaveCounts wc, uint32_t bounce, float* __restrict__ wave_out) {
+          ShadowRays sh, uint32_t* __restrict__ queues, WaveCounts wc, uint32_t bounce, float* __restrict__ wave_out,
+          TraceCounters* __restrict__ counters) {
     const uint32_t n = wc.active[bounce];
+    uint32_t n_culled = 0;
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t iters = (n + stride - 1) / stride;
     const DeviceTexFetch tex{sc.textures};
@@ -105,6 +108,7 @@ k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restri
     for (uint32_t it = 0; it < iters; it++) {
         const uint32_t i = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
         int kind = -1;
+        bool culled = false;
         if (i < n) {
             const float4 hv = reinterpret_cast<const float4*>(hits)[i];
             HitRecord hit;
@@ -132,10 +136,34 @@ k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restri
                 sf.rough[i] = s.sp.roughness;
                 sf.info[i] = (s.light >= 0 ? ((uint32_t)s.light | kInfoHasLight) : 0u) |
                              (s.conductor ? kInfoConductor : 0u);
+                kind = wp.mode == B2PT_BSDF_AUTO ? (s.conductor ? kBsdfConductor : kBsdfLayered) : wp.mode - 1;
+                // Shadow rays whose answer cannot matter are not traced.  The reference traces every one
+                // (LightVisibility, :216-241) and then multiplies by f(wo, wl); for the three BSDFs whose f
+                // draws no random numbers, f is EXACTLY zero when the material is a perfect mirror /
+                // smooth glass (alpha < 1e-3) or, for the opaque ones, when wo and wl lie on opposite
+                // sides of the shading normal — the first tests of conductor_f / diffuse_f /
+                // dielectric_f (bsdf.cuh), evaluated here with the same operands shade_stage will use
+                // (to_local(...).z = dot(n, v), wl = the shadow direction).  Leaving `visible` unset makes
+                // shade_stage skip the same zero.  The layered BSDF is excluded: its f consumes draws,
+                // so whether it runs must follow the reference.  Output bits are unchanged; the counter
+                // `shadow_rays` keeps the reference's count, `shadow_rays_traced` is what K8 really ran.
+                bool trace_shadow = s.sh_tmax >= 0.0f;
+                if (trace_shadow && kind != kBsdfLayered) {
+                    const float3 ray_d = v3(st.dx[i], st.dy[i], st.dz[i]);
+                    const float wo_z = dot(s.ns, normalize(-ray_d)), wl_z = dot(s.ns, s.sh_d);
+                    const bool smooth = effectively_smooth(roughness_to_alpha(s.sp.roughness));
+                    const bool opposite = !(wo_z * wl_z > 0.0f);   // !same_hemisphere(wo, wl)
+                    const bool zero_f = kind == kBsdfConductor ? (smooth || opposite)
+                                      : kind == kBsdfDiffuse   ? opposite
+                                                               : smooth;   // dielectric
+                    if (zero_f && wp.cull_nee) {
+                        trace_shadow = false;
+                        culled = true;
+                    }
+                }
                 sh.ox[i] = s.sh_o.x; sh.oy[i] = s.sh_o.y; sh.oz[i] = s.sh_o.z;
                 sh.dx[i] = s.sh_d.x; sh.dy[i] = s.sh_d.y; sh.dz[i] = s.sh_d.z;
-                sh.tmax[i] = s.sh_tmax;
-                kind = wp.mode == B2PT_BSDF_AUTO ? (s.conductor ? kBsdfConductor : kBsdfLayered) : wp.mode - 1;
+                sh.tmax[i] = trace_shadow ? s.sh_tmax : -1.0f;
             }
         }
 #pragma unroll
@@ -143,7 +171,10 @@ k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restri
             const uint32_t pos = warp_append(kind == k, qn + k);
             if (kind == k) queues[(size_t)k * wp.capacity + pos] = i;
         }
+        n_culled += culled ? 1u : 0u;
     }
+    for (int off = 16; off > 0; off >>= 1) n_culled += __shfl_xor_sync(0xffffffffu, n_culled, off);
+    if ((threadIdx.x & 31) == 0 && n_culled) atomicAdd(&counters->shadow_culled, (unsigned long long)n_culled);
 }
 
 // ---- K7a-d -------------------------------------------------------------------
@@ -342,7 +373,7 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
         launch_closest(lc, sc, cur, wc.active + b, 0.0f, 100.0f, r->d_hits.get(), r->d_counters.get());   // tmin 0, tmax 100 (:652)
         mark(kClsClosest);
         k_surface<Rng><<<grid, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
-                                                 wc, (uint32_t)b, r->d_wave_out.get());
+                                                 wc, (uint32_t)b, r->d_wave_out.get(), r->d_counters.get());
         count();
         mark(kClsSurface);
         if (wp.n_lights > 0) {
@@ -401,6 +432,8 @@ void render_frames(B2ptRenderer* r, int spp, bool accumulate) {
     wp.mode = r->cfg.bsdf_mode;
     wp.seed = r->cfg.seed;
     wp.capacity = capacity;
+    static const int cull_nee = [] { const char* e = getenv("B2PT_CULL_NEE"); return e ? atoi(e) : 1; }();
+    wp.cull_nee = cull_nee;
     float* dst = accumulate ? r->d_accum.get() : r->d_frame.get();
 
     r->timing_used = 0;
