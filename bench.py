@@ -191,7 +191,9 @@ def algorithmic_bytes_per_ray(scene, w, h, depth, mode, spp=1):
             "tris_per_ray": st["triangles_tested"] / rr, "exact_per_ray": st["exact_tests"] / rr,
             "nodes_per_shadow_ray": st["nodes_visited_shadow"] / sr, "tris_per_shadow_ray": st["triangles_tested_shadow"] / sr,
             "rays_per_sample": (st["radiance_rays"] + st["shadow_rays_traced"]) / max(st["samples"], 1),
-            "shadow_rays_culled_frac": 1.0 - st["shadow_rays_traced"] / max(st["shadow_rays"], 1)}
+            "shadow_rays_culled_frac": 1.0 - st["shadow_rays_traced"] / max(st["shadow_rays"], 1),
+            "simd_node_loop": st["nodes_visited"] / max(st["warp_slots_node"], 1),
+            "simd_tri_loop": st["triangles_tested"] / max(st["warp_slots_tri"], 1)}
 
 
 class DevicePtr:
@@ -329,6 +331,7 @@ def run_b2pt(args, cfg):
     roofline = {"kernel": "k_closest (K5 closest-hit BVH traversal)", "bound": "hbm", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "bytes_per_ray": bpr["closest"], "nodes_per_ray": bpr["nodes_per_ray"], "tris_per_ray": bpr["tris_per_ray"],
+                "simd_node_loop": bpr["simd_node_loop"], "simd_tri_loop": bpr["simd_tri_loop"],
                 "bytes_per_launch": st["radiance_rays"] * bpr["closest"] / max(n_k[0], 1),
                 "ms_per_launch": closest_ms / max(n_k[0], 1), "launches": n_k[0],
                 "share_of_step": {"closest": ms_k[0] / render_ms, "any": ms_k[1] / render_ms, "surface": ms_k[2] / render_ms,

@@ -157,6 +157,11 @@ typedef struct B2ptStats {
      * light is exactly zero (mirror / smooth glass, light behind an opaque surface) and which
      * K6 therefore never emits — same image, fewer rays.             */
     uint64_t shadow_rays_traced;
+    /* K5 with collect_stats: lane slots issued by the node loop and the triangle loop of the
+     * warp-persistent kernel (32 per warp trip).  nodes_visited / warp_slots_node and
+     * triangles_tested / warp_slots_tri are the SIMD utilisation of the two loops.          */
+    uint64_t warp_slots_node;
+    uint64_t warp_slots_tri;
 } B2ptStats;
 
 typedef struct B2ptRenderer B2ptRenderer;

@@ -66,7 +66,8 @@ class B2ptStats(C.Structure):
                 ("nodes_visited_shadow", C.c_uint64), ("triangles_tested_shadow", C.c_uint64),
                 ("exact_tests_shadow", C.c_uint64),
                 ("device_ms_kernel", C.c_double * 5), ("launches_kernel", C.c_uint64 * 5),
-                ("shadow_rays_traced", C.c_uint64)]
+                ("shadow_rays_traced", C.c_uint64), ("warp_slots_node", C.c_uint64),
+                ("warp_slots_tri", C.c_uint64)]
 
 
 # name -> (restype, argtypes); exactly the symbols include/b2pt.h declares.

@@ -315,6 +315,8 @@ int b2pt_get_stats(const B2ptRenderer* rc, B2ptStats* out) {
             out->launches_kernel[k] = r->launches_kernel_cls[k];
         }
         out->shadow_rays_traced = out->shadow_rays - c.shadow_culled;
+        out->warp_slots_node = c.node_slots;
+        out->warp_slots_tri = c.tri_slots;
     });
 }
 

@@ -149,7 +149,7 @@ B2PT_HD Cplx csqrt(Cplx z) {
     return {fabsf(t2), copysignf(t1, z.im)};
 }
 // Fresnel reflectance of a conductor with complex IOR eta + i k (Conductor.h:42-52)
-B2PT_HD float fresnel_complex_1(float cos_i, Cplx eta) {
+B2PT_HD_CALL float fresnel_complex_1(float cos_i, Cplx eta) {
     cos_i = clampf(cos_i, 0.0f, 1.0f);
     const Cplx ci = {cos_i, 0.0f};
     const float s2i = 1.0f - sqr(cos_i);
@@ -162,7 +162,7 @@ B2PT_HD float fresnel_complex_1(float cos_i, Cplx eta) {
 }
 // per channel, IOR derived from the reflectance colour (Conductor.h:54-93):
 // eta = 1, k = 2 sqrt(r) / sqrt(1 - r), r clamped to [0, .9999]
-B2PT_HD float3 fresnel_conductor(float cos_i, float3 reflectance) {
+B2PT_HD_CALL float3 fresnel_conductor(float cos_i, float3 reflectance) {
     const float3 r = v3(clampf(reflectance.x, 0.0f, 0.9999f), clampf(reflectance.y, 0.0f, 0.9999f),
                         clampf(reflectance.z, 0.0f, 0.9999f));
     const float kx = 2.0f * sqrtf(r.x) / sqrtf(fmaxf(1.0f - r.x, 0.0f));

@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(kTraceThreads)
 k_closest(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active, float tmin, float tmax,
           HitRecord* __restrict__ hits, TraceCounters* counters) {
     const uint32_t n = *n_active;
-    TraceStats ts = {0, 0, 0};
+    TraceStats ts = {0, 0, 0, 0, 0};
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float3 o = v3(st.ox[i], st.oy[i], st.oz[i]);
         const float3 d = v3(st.dx[i], st.dy[i], st.dz[i]);
@@ -40,6 +40,8 @@ k_closest(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active, f
         atomicAdd(&counters->nodes, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris, (unsigned long long)ts.tris);
         atomicAdd(&counters->exact, (unsigned long long)ts.exact);
+        atomicAdd(&counters->node_slots, (unsigned long long)ts.node_slots);
+        atomicAdd(&counters->tri_slots, (unsigned long long)ts.tri_slots);
     }
 }
 
@@ -48,7 +50,7 @@ __global__ void __launch_bounds__(kTraceThreads)
 k_any(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, float tmin,
       uint32_t* __restrict__ info, uint8_t* __restrict__ occluded, TraceCounters* counters) {
     const uint32_t n = *n_active;
-    TraceStats ts = {0, 0, 0};
+    TraceStats ts = {0, 0, 0, 0, 0};
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float tmax = sh.tmax[i];
         if (!(tmax >= 0.0f)) continue;  // no shadow ray for this slot
@@ -106,7 +108,7 @@ template <bool STATS, bool ALPHA, int MINB = 4>
 __global__ void __launch_bounds__(kTraceThreads, MINB)
 k_closest_p(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active, float tmin, float tmax,
             HitRecord* __restrict__ hits, TraceCounters* counters, WarpPolicy pol) {
-    TraceStats ts = {0, 0, 0};
+    TraceStats ts = {0, 0, 0, 0, 0};
     const ClosestIo io{st, hits, tmax};
     if (ALPHA)
         trace_persistent<false, STATS>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io,
@@ -117,6 +119,8 @@ k_closest_p(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active,
         atomicAdd(&counters->nodes, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris, (unsigned long long)ts.tris);
         atomicAdd(&counters->exact, (unsigned long long)ts.exact);
+        atomicAdd(&counters->node_slots, (unsigned long long)ts.node_slots);
+        atomicAdd(&counters->tri_slots, (unsigned long long)ts.tri_slots);
     }
 }
 
@@ -124,7 +128,7 @@ template <bool STATS, bool ALPHA, int MINB = 4>
 __global__ void __launch_bounds__(kTraceThreads, MINB)
 k_any_p(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, float tmin,
         uint32_t* __restrict__ info, uint8_t* __restrict__ occluded, TraceCounters* counters, WarpPolicy pol) {
-    TraceStats ts = {0, 0, 0};
+    TraceStats ts = {0, 0, 0, 0, 0};
     const AnyIo io{sh, info, occluded};
     if (ALPHA)
         trace_persistent<true, STATS>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io,

@@ -120,6 +120,7 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
             // the warp descends together; a lane stops with a second leaf in `node`, or done, and
             // the warp leaves the descent once break_lanes lanes have stopped
             while (true) {
+              if (STATS) ts.node_slots++;
               if (node >= 0 && node != kStackSentinel) {
                 if (STATS) ts.nodes++;
                 const BvhNode2* np = nodes + node;
@@ -151,6 +152,7 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
               if ((int)__popc(__ballot_sync(kFullMask, stopped)) >= pol.break_lanes) break;
             }
             // all lanes test their postponed triangles
+            const uint32_t tris_before = ts.tris;
             while (pend < 0) {
                 const int slot = ~pend;
                 pend = 0;
@@ -193,6 +195,7 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
                     node = B2PT_POP();
                 }
             }
+            if (STATS) ts.tri_slots += __reduce_max_sync(kFullMask, ts.tris - tris_before);   // summed over lanes: 32 x warp trips
         } while ((int)__popc(__ballot_sync(kFullMask, node == kStackSentinel)) < kRefill);
     }
 }

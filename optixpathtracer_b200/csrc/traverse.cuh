@@ -32,6 +32,7 @@ namespace b2pt {
 
 struct TraceStats {
     uint32_t nodes, tris, exact;
+    uint32_t node_slots, tri_slots;   // persistent kernels: lane slots (32 per warp trip) of the node / triangle loops
 };
 
 // fp64 Moeller-Trumbore, the deciding test.  Operation order is part of the

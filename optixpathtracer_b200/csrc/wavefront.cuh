@@ -56,6 +56,7 @@ constexpr int kShadowWords = 7;
 struct TraceCounters {
     unsigned long long nodes, tris, exact, radiance_rays, shadow_rays, nan_samples;
     unsigned long long nodes_any, tris_any, exact_any;
+    unsigned long long node_slots, tri_slots;   // K5 stats build: lane slots of the node / triangle loops
     unsigned long long shadow_culled;   // shadow rays K6 did not emit because f(wo, wl) is exactly zero
 };
 enum KernelClass : int { kClsClosest = 0, kClsAny = 1, kClsSurface = 2, kClsShade = 3, kClsOther = 4, kClsCount = 5 };
