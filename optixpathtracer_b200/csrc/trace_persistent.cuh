@@ -20,9 +20,48 @@
 // existence test.
 #pragma once
 
+#include <type_traits>
+
 #include "traverse.cuh"
 
 namespace b2pt {
+
+// tri_filter (traverse.cuh) with one more answer.  0: the fp64 test is guaranteed to reject (or to land
+// outside (tmin, tbest]); 1: undecided, run it; 2: it is guaranteed to ACCEPT with t inside
+// (tmin, tbest) — the fp32 barycentrics and distance clear their error bounds on the inside, evaluated
+// with directed rounding.  The margins K * (...) bound |fp32 value - real value|; the fp64 evaluation
+// differs from the real value by ~1e-16 of the same magnitudes, far inside them.
+__device__ __forceinline__ int tri_classify(float3 o, float3 d, float d_l1, float3 v0, float3 v1, float3 v2,
+                                            float tmin, float tbest) {
+    const float K = 1.9073486e-6f;
+    const float3 e1 = v1 - v0, e2 = v2 - v0, tv = o - v0;
+    const float3 p = cross(d, e2);
+    const float det = dot(e1, p);
+    const float a1 = fabsf(e1.x) + fabsf(e1.y) + fabsf(e1.z);
+    const float a2 = fabsf(e2.x) + fabsf(e2.y) + fabsf(e2.z);
+    const float at = fabsf(tv.x) + fabsf(tv.y) + fabsf(tv.z);
+    const float err_det = K * a1 * a2 * d_l1;
+    const float D = fabsf(det);
+    if (!(D > err_det)) return 1;  // grazing / degenerate: let fp64 decide
+    const float sgn = det < 0.0f ? -1.0f : 1.0f;
+    const float err_u = K * at * a2 * d_l1;
+    const float U = dot(tv, p) * sgn;
+    if (U < -err_u) return 0;
+    const float3 q = cross(tv, e1);
+    const float err_v = K * at * a1 * d_l1;
+    const float V = dot(d, q) * sgn;
+    if (V < -err_v) return 0;
+    const float err_uv = err_det + err_u + err_v;
+    if (U + V > D + err_uv) return 0;
+    const float err_t = K * at * a1 * a2;
+    const float T = dot(e2, q) * sgn;
+    if (T + err_t < tmin * (D - err_det)) return 0;
+    if (T - err_t > tbest * (D + err_det)) return 0;
+    const float d_lo = __fadd_rd(D, -err_det), d_hi = __fadd_ru(D, err_det);
+    const bool inside = U > err_u && V > err_v && __fadd_ru(__fadd_ru(U, V), err_uv) < D && d_lo > 0.0f &&
+                        __fadd_rd(T, -err_t) > __fmul_ru(tmin, d_hi) && __fadd_ru(T, err_t) < __fmul_rd(tbest, d_lo);
+    return inside ? 2 : 1;
+}
 
 constexpr uint32_t kFullMask = 0xffffffffu;
 constexpr uint32_t kRayChunk = 64;
@@ -162,7 +201,17 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
                 const float4 tb = B2PT_LDG4(&tp->b);
                 const float4 tc = B2PT_LDG4(&tp->c);
                 const float3 v0 = v3(ta.x, ta.y, ta.z), v1 = v3(ta.w, tb.x, tb.y), v2 = v3(tb.z, tb.w, tc.x);
-                if (tri_filter(r.o, r.d, r.d_l1, v0, v1, v2, tmin, best32)) {
+                // shadow rays without an any-hit predicate: a triangle the fp32 test PROVES to be hit inside
+                // (tmin, tmax) occludes without the fp64 test (closest hits still need its t, u, v)
+                constexpr bool kProven = ANY && std::is_same<Accept, AcceptAllHits>::value;
+                const int cls = kProven ? tri_classify(r.o, r.d, r.d_l1, v0, v1, v2, tmin, best32)
+                                        : (tri_filter(r.o, r.d, r.d_l1, v0, v1, v2, tmin, best32) ? 1 : 0);
+                if (kProven && cls == 2) {
+                    occluded = true;
+                    node = kStackSentinel;
+                    break;
+                }
+                if (cls != 0) {
                     if (STATS) ts.exact++;
                     double t, u, v;
                     bool bf;
