@@ -8,7 +8,7 @@
 #include "wavefront.cuh"
 #include "traverse.cuh"
 #include "alpha.cuh"
-#include "trace_persistent.cuh"
+#include "trace_deferred.cuh"
 
 #include <cstdlib>
 
@@ -84,6 +84,10 @@ struct ClosestIo {
     __device__ __forceinline__ void store(uint32_t i, const HitRecord& h, bool) const {
         reinterpret_cast<float4*>(hits)[i] = make_float4(__uint_as_float(h.tri), h.t, h.u, h.v);
     }
+    // deferred mode: only the triangle; t, u, v, back-face flag are evaluated by the consumer
+    __device__ __forceinline__ void store_slot(uint32_t i, int slot) const {
+        reinterpret_cast<float4*>(hits)[i] = make_float4(__uint_as_float(slot < 0 ? kHitMiss : (uint32_t)slot), 0.0f, 0.0f, 0.0f);
+    }
     float tmax;
 };
 struct AnyIo {
@@ -103,6 +107,35 @@ struct AnyIo {
     }
 };
 
+
+// K5 without the fp64 test (trace_deferred.cuh); scenes without an any-hit predicate only
+template <bool STATS, int MINB = 4>
+__global__ void __launch_bounds__(kTraceThreads, MINB)
+k_closest_d(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active, float tmin, float tmax,
+            HitRecord* __restrict__ hits, TraceCounters* counters, WarpPolicy pol) {
+    TraceStats ts = {0, 0, 0, 0, 0};
+    const ClosestIo io{st, hits, tmax};
+    trace_closest_deferred<STATS>(sc.nodes, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
+    if (STATS) {
+        atomicAdd(&counters->nodes, (unsigned long long)ts.nodes);
+        atomicAdd(&counters->tris, (unsigned long long)ts.tris);
+        atomicAdd(&counters->exact, (unsigned long long)ts.exact);
+        atomicAdd(&counters->node_slots, (unsigned long long)ts.node_slots);
+        atomicAdd(&counters->tri_slots, (unsigned long long)ts.tri_slots);
+    }
+}
+
+// the fp64 evaluation of the hits k_closest_d found: t, u, v and the back-face flag (parity hooks;
+// the renderer does this inside k_surface)
+__global__ void __launch_bounds__(256)
+k_finish_hits(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active, HitRecord* __restrict__ hits) {
+    const uint32_t n = *n_active;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t slot = hits[i].tri;
+        if (slot == kHitMiss) continue;
+        hits[i] = finish_hit(sc.tris, slot, v3(st.ox[i], st.oy[i], st.oz[i]), v3(st.dx[i], st.dy[i], st.dz[i]));
+    }
+}
 
 template <bool STATS, bool ALPHA, int MINB = 4>
 __global__ void __launch_bounds__(kTraceThreads, MINB)
@@ -155,6 +188,10 @@ WarpPolicy warp_policy() {
     }();
     return v;
 }
+bool use_deferred() {   // B2PT_DEFER=0: fp64 tests inside K5 (trace_persistent), for A/B measurements
+    static const bool v = [] { const char* e = getenv("B2PT_DEFER"); return !(e && e[0] == '0'); }();
+    return v;
+}
 bool use_persistent() {
     static const bool v = [] { const char* e = getenv("B2PT_TRAVERSAL"); return !(e && e[0] == '0'); }();
     return v;
@@ -166,8 +203,24 @@ int trace_grid_blocks_per_sm() { return occ_blocks() > 0 ? occ_blocks() : 8; }
 
 void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState& st,
                     const uint32_t* n_active, float tmin, float tmax, HitRecord* hits,
-                    TraceCounters* counters) {
+                    TraceCounters* counters, bool finish) {
     const bool alpha = sc.any_alpha_texture != 0;
+    if (use_persistent() && use_deferred() && !alpha) {
+        if (lc.stats)
+            k_closest_d<true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (occ_blocks() == 8)
+            k_closest_d<false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (occ_blocks() == 6)
+            k_closest_d<false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else
+            k_closest_d<false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        if (lc.launch_counter) ++*lc.launch_counter;
+        if (finish) {
+            k_finish_hits<<<lc.grid, 256, 0, lc.stream>>>(sc, st, n_active, hits);
+            if (lc.launch_counter) ++*lc.launch_counter;
+        }
+        return;
+    }
     if (use_persistent()) {
         if (lc.stats && alpha)
             k_closest_p<true, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());

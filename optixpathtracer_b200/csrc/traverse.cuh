@@ -100,6 +100,26 @@ B2PT_HD bool tri_filter(float3 o, float3 d, float d_l1, float3 v0, float3 v1, fl
     return true;
 }
 
+// t, u, v and the back-face flag of a known hit: the fp64 evaluation of triangle `slot` (the
+// deferred K5 stores only the slot, trace_deferred.cuh)
+B2PT_HD HitRecord finish_hit(const TriRecord* __restrict__ tris, uint32_t slot, float3 o, float3 d) {
+    const TriRecord* tp = tris + slot;
+    const float4 ta = B2PT_LDG4(&tp->a), tb = B2PT_LDG4(&tp->b), tc = B2PT_LDG4(&tp->c);
+    double t, u, v;
+    bool bf = false;
+    HitRecord h;
+    if (tri_exact(o, d, v3(ta.x, ta.y, ta.z), v3(ta.w, tb.x, tb.y), v3(tb.z, tb.w, tc.x), t, u, v, bf)) {
+        h.tri = slot | (bf ? kHitBackface : 0u);
+        h.t = (float)t;
+        h.u = (float)u;
+        h.v = (float)v;
+    } else {   // cannot happen for a slot the traversal proved hit; a miss is the safe reading
+        h.tri = kHitMiss;
+        h.t = h.u = h.v = 0.0f;
+    }
+    return h;
+}
+
 struct RaySetup {
     float3 o, d, idir;
     float d_l1;

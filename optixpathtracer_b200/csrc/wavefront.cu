@@ -26,6 +26,7 @@
 
 #include "render.h"
 #include "integrator.cuh"
+#include "traverse.cuh"
 
 namespace b2pt {
 
@@ -110,9 +111,14 @@ k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restri
         int kind = -1;
         bool culled = false;
         if (i < n) {
-            const float4 hv = reinterpret_cast<const float4*>(hits)[i];
             HitRecord hit;
-            hit.tri = __float_as_uint(hv.x); hit.t = hv.y; hit.u = hv.z; hit.v = hv.w;
+            hit.tri = hits[i].tri;
+            hit.t = hit.u = hit.v = 0.0f;
+            // K5 decided WHICH triangle is hit (trace_deferred.cuh); its t, u, v and back-face flag — the
+            // fp64 evaluation of that one triangle — are computed here, where every lane has a hit
+            if (hit.tri != kHitMiss)
+                hit = finish_hit(sc.tris, hit.tri & ~kHitBackface, v3(st.ox[i], st.oy[i], st.oz[i]),
+                                 v3(st.dx[i], st.dy[i], st.dz[i]));
             if (hit.tri == kHitMiss) {   // __miss__radiance (:576-583): the path ends with what it has
                 const uint32_t id = st.id[i];
                 wave_out[id] = st.rx[i];
@@ -370,7 +376,7 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
     for (int b = 0; b < wp.max_bounces; b++) {
         const PathState& cur = r->st[b & 1];
         const PathState& nxt = r->st[(b + 1) & 1];
-        launch_closest(lc, sc, cur, wc.active + b, 0.0f, 100.0f, r->d_hits.get(), r->d_counters.get());   // tmin 0, tmax 100 (:652)
+        launch_closest(lc, sc, cur, wc.active + b, 0.0f, 100.0f, r->d_hits.get(), r->d_counters.get(), /*finish=*/false);   // tmin 0, tmax 100 (:652)
         mark(kClsClosest);
         k_surface<Rng><<<grid, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
                                                  wc, (uint32_t)b, r->d_wave_out.get(), r->d_counters.get());

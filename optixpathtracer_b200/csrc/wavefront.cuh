@@ -75,7 +75,9 @@ int trace_grid_blocks_per_sm();
 // K5: closest hit for rays [0, *n_active) of `st`; n_active lives on the device.
 void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState& st,
                     const uint32_t* n_active, float tmin, float tmax, HitRecord* hits,
-                    TraceCounters* counters);
+                    TraceCounters* counters, bool finish = true);
+// finish = false: the caller evaluates t, u, v and the back-face flag of the stored triangle itself
+// (finish_hit, traverse.cuh) — k_surface does; true adds k_finish_hits after the deferred K5.
 // K8: any hit for shadow rays [0, *n_active); sets kInfoVisible in info[] (if
 // info != nullptr) and/or occluded[] (if non-null).
 void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh,

@@ -104,6 +104,33 @@ def test_tiny_and_empty_scenes(oracle):
         assert r.Stats()["n_nodes"] == 0
 
 
+def test_rays_through_mesh_vertices_and_edges(oracle):
+    """The deferred K5 orders hits by fp32 intervals and falls back to fp64 when intervals overlap: aim
+    rays at the shared vertices and edge midpoints of a closed tessellated mesh (and a hair beside them),
+    where two to six triangles are hit at the same distance, and through two coincident shells."""
+    from optixpathtracer_b200 import scenes as S
+    pos, _, _, idx = S.uv_sphere(24, 12)
+    tri = pos[idx].astype(f32)                                   # (n, 3, 3)
+    soup = np.concatenate([tri, tri * f32(1.0), tri[::-1] * f32(2.0)]).astype(f32)   # duplicate shell + outer shell
+    rng = np.random.default_rng(21)
+    verts = pos.astype(np.float64)
+    mids = 0.5 * (tri[:, 0].astype(np.float64) + tri[:, 1].astype(np.float64))
+    targets = np.concatenate([verts, mids, verts + rng.normal(scale=1e-7, size=verts.shape),
+                              mids + rng.normal(scale=1e-7, size=mids.shape)])
+    org = rng.normal(size=targets.shape)
+    org = 5.0 * org / np.linalg.norm(org, axis=1, keepdims=True)
+    inside = rng.random(len(targets)) < 0.3                     # some rays start inside (back faces first)
+    org[inside] *= 0.02
+    d = targets - org
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    o, d = org.astype(f32), d.astype(f32)
+    with _renderer(_soup_scene(soup)) as r:
+        _compare(r, oracle, soup, o, d, 0.0, 100.0)
+        _compare(r, oracle, soup, o, d, 0.5, 5.2)
+        tm = np.full(len(o), 4.5, f32)
+        assert np.array_equal(r.TraceAny(o, d, tm), oracle.any(soup, o, d, tm))
+
+
 def test_far_origins_small_triangles(oracle):
     rng = np.random.default_rng(11)
     c = rng.uniform(-1, 1, (4000, 1, 3))
