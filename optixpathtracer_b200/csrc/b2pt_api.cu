@@ -304,7 +304,7 @@ int b2pt_get_stats(const B2ptRenderer* rc, B2ptStats* out) {
         out->device_ms_build = r->scene.build_ms;
         out->n_triangles = r->scene.n_tris;
         out->n_nodes = r->scene.n_nodes;
-        out->node_bytes = (int32_t)sizeof(BvhNode2);
+        out->node_bytes = trace_node_bytes(r->scene.view());
         out->triangle_bytes = (int32_t)sizeof(TriRecord);
         out->scene_device_bytes = r->scene.device_bytes();
         out->nodes_visited_shadow = c.nodes_any;

@@ -37,6 +37,19 @@ struct alignas(16) BvhNode2 {
 };
 static_assert(sizeof(BvhNode2) == 64, "node must be 64 bytes");
 
+// 4-wide node (K5/K8 read this one): the four grandchildren of binary node i — or a child itself where
+// that child is a leaf — stored per axis across the four slots, so a visit is 7 x LDG.128 and covers two
+// levels of the binary tree in one dependent step.  Entry i exists for every binary node (same index), the
+// traversal from the root only ever reaches the even-depth ones.  Empty slots have the box
+// lo = hi = +inf (never hit) and child = kEmptyChild.
+struct alignas(16) BvhNode4 {
+    float4 lox, hix, loy, hiy, loz, hiz;   // component k = slot k
+    int32_t child[4];                      // >= 0: binary node index (= BvhNode4 index); < 0: ~(triangle slot)
+    int32_t pad[4];
+};
+static_assert(sizeof(BvhNode4) == 128, "wide node must be 128 bytes");
+constexpr int32_t kEmptyChild = 0x7ffffffe;
+
 struct alignas(16) TriRecord {
     float4 a;   // v0.x v0.y v0.z v1.x
     float4 b;   // v1.y v1.z v2.x v2.y

@@ -289,6 +289,45 @@ k_emit_nodes(int n, const float3* __restrict__ wv, const uint32_t* __restrict__ 
     nodes[i] = nd;
 }
 
+// ---- K3d: collapse two binary levels into one 4-wide node ---------------------------
+__global__ void __launch_bounds__(kThreads)
+k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restrict__ wide) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    const BvhNode2 nd = nodes[i];
+    float lo[3][4], hi[3][4];
+    int32_t ch[4];
+    int k = 0;
+    auto put = [&](float lx, float hx, float ly, float hy, float lz, float hz, int32_t c) {
+        lo[0][k] = lx; hi[0][k] = hx; lo[1][k] = ly; hi[1][k] = hy; lo[2][k] = lz; hi[2][k] = hz;
+        ch[k] = c;
+        k++;
+    };
+#pragma unroll
+    for (int s = 0; s < 2; s++) {
+        const int32_t c = s ? nd.child1 : nd.child0;
+        const float4 xy = s ? nd.c1xy : nd.c0xy;
+        const float lz = s ? nd.cz.z : nd.cz.x, hz = s ? nd.cz.w : nd.cz.y;
+        if (c < 0 || !(xy.x <= xy.y)) {            // a leaf (or the never-hit slot of a one-triangle scene) stays one slot
+            if (xy.x <= xy.y) put(xy.x, xy.y, xy.z, xy.w, lz, hz, c);
+        } else {                                    // an internal child contributes its two children
+            const BvhNode2 g = nodes[c];
+            put(g.c0xy.x, g.c0xy.y, g.c0xy.z, g.c0xy.w, g.cz.x, g.cz.y, g.child0);
+            put(g.c1xy.x, g.c1xy.y, g.c1xy.z, g.c1xy.w, g.cz.z, g.cz.w, g.child1);
+        }
+    }
+    // empty slot: lo = hi = +inf fails the slab test for every direction (an INVERTED box would pass it:
+    // min(+inf, -inf) = -inf <= max = +inf)
+    for (; k < 4;) put(INFINITY, INFINITY, INFINITY, INFINITY, INFINITY, INFINITY, kEmptyChild);
+    BvhNode4 w;
+    w.lox = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]); w.hix = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
+    w.loy = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]); w.hiy = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]);
+    w.loz = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); w.hiz = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
+#pragma unroll
+    for (int j = 0; j < 4; j++) { w.child[j] = ch[j]; w.pad[j] = 0; }
+    wide[i] = w;
+}
+
 // single-triangle scene: one node, second child never hit
 __global__ void k_emit_single(const float3* __restrict__ wv, float pad, BvhNode2* __restrict__ nodes) {
     const Aabb b = leaf_box(wv, 0, pad);
@@ -344,6 +383,7 @@ k_emit_tris(int n, const float3* __restrict__ wv, const float* __restrict__ norm
 DeviceScene SceneBuffers::view() const {
     DeviceScene s;
     s.nodes = nodes.get();
+    s.nodes4 = nodes4.get();
     s.tris = tris.get();
     s.nrms = nrms.get();
     s.uvs = uvs.get();
@@ -358,7 +398,7 @@ DeviceScene SceneBuffers::view() const {
 }
 
 int64_t SceneBuffers::device_bytes() const {
-    return (int64_t)(nodes.bytes() + tris.bytes() + nrms.bytes() + uvs.bytes() + materials.bytes() +
+    return (int64_t)(nodes.bytes() + nodes4.bytes() + tris.bytes() + nrms.bytes() + uvs.bytes() + materials.bytes() +
                      textures.bytes() + tri_order.bytes());
 }
 
@@ -472,6 +512,7 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
     create_textures(desc, out, stream);
     out.n_nodes = n == 0 ? 0 : (n == 1 ? 1 : n - 1);
     out.nodes.alloc((size_t)out.n_nodes);
+    out.nodes4.alloc((size_t)out.n_nodes);
     out.tris.alloc((size_t)n);
     out.nrms.alloc((size_t)n);
     out.uvs.alloc(any_uv ? (size_t)n : 0);
@@ -559,6 +600,8 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
     } else {
         k_emit_single<<<1, 1, 0, stream>>>(d_wv.get(), pad, out.nodes.get());
     }
+    if (out.n_nodes > 0)
+        k_collapse4<<<blocks_for(out.n_nodes), kThreads, 0, stream>>>(out.n_nodes, out.nodes.get(), out.nodes4.get());
     k_emit_tris<<<blocks_for(n), kThreads, 0, stream>>>(n, d_wv.get(), d_nrm.get(), order, d_tri_mesh.get(),
                                                          d_infos.get(), d_idx.get(), d_uv.get(),
                                                          out.tris.get(), out.nrms.get(), out.uvs.get());

@@ -43,6 +43,7 @@ struct MeshInfo {
 // POD view handed to kernels by value.
 struct DeviceScene {
     const BvhNode2* nodes;
+    const BvhNode4* nodes4;         // the same tree, two levels per node (bvh.cuh)
     const TriRecord* tris;
     const NrmRecord* nrms;
     const UvRecord* uvs;            // nullptr when no mesh has texcoords
@@ -57,6 +58,7 @@ struct DeviceScene {
 
 struct SceneBuffers {
     DeviceBuffer<BvhNode2> nodes;
+    DeviceBuffer<BvhNode4> nodes4;
     DeviceBuffer<TriRecord> tris;
     DeviceBuffer<NrmRecord> nrms;
     DeviceBuffer<UvRecord> uvs;

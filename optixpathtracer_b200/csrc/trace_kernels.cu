@@ -8,7 +8,7 @@
 #include "wavefront.cuh"
 #include "traverse.cuh"
 #include "alpha.cuh"
-#include "trace_deferred.cuh"
+#include "trace_wide.cuh"
 
 #include <cstdlib>
 
@@ -125,6 +125,36 @@ k_closest_d(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active,
     }
 }
 
+// K5 / K8 over the 4-wide nodes (trace_wide.cuh)
+template <bool STATS, int MINB = 4>
+__global__ void __launch_bounds__(kTraceThreads, MINB)
+k_closest_w(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active, float tmin, float tmax,
+            HitRecord* __restrict__ hits, TraceCounters* counters, WarpPolicy pol) {
+    TraceStats ts = {0, 0, 0, 0, 0};
+    const ClosestIo io{st, hits, tmax};
+    trace_wide<false, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
+    if (STATS) {
+        atomicAdd(&counters->nodes, (unsigned long long)ts.nodes);
+        atomicAdd(&counters->tris, (unsigned long long)ts.tris);
+        atomicAdd(&counters->exact, (unsigned long long)ts.exact);
+        atomicAdd(&counters->node_slots, (unsigned long long)ts.node_slots);
+        atomicAdd(&counters->tri_slots, (unsigned long long)ts.tri_slots);
+    }
+}
+template <bool STATS, int MINB = 4>
+__global__ void __launch_bounds__(kTraceThreads, MINB)
+k_any_w(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, float tmin, uint32_t* info,
+        uint8_t* occluded, TraceCounters* counters, WarpPolicy pol) {
+    TraceStats ts = {0, 0, 0, 0, 0};
+    const AnyIo io{sh, info, occluded};
+    trace_wide<true, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
+    if (STATS) {
+        atomicAdd(&counters->nodes_any, (unsigned long long)ts.nodes);
+        atomicAdd(&counters->tris_any, (unsigned long long)ts.tris);
+        atomicAdd(&counters->exact_any, (unsigned long long)ts.exact);
+    }
+}
+
 // the fp64 evaluation of the hits k_closest_d found: t, u, v and the back-face flag (parity hooks;
 // the renderer does this inside k_surface)
 __global__ void __launch_bounds__(256)
@@ -176,8 +206,9 @@ k_any_p(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, fl
 }
 
 // B2PT_TRAVERSAL=0 selects the first (thread-per-ray) kernels, for A/B measurements
-int occ_blocks() {
-    static const int v = [] { const char* e = getenv("B2PT_OCC"); return e ? atoi(e) : 8; }();
+bool use_wide();
+int occ_blocks() {   // resident blocks per SM the traversal kernels are built and launched for
+    static const int v = [] { const char* e = getenv("B2PT_OCC"); return e ? atoi(e) : (use_wide() ? 6 : 8); }();
     return v;
 }
 WarpPolicy warp_policy() {
@@ -186,6 +217,10 @@ WarpPolicy warp_policy() {
         const char* b = getenv("B2PT_BREAK");
         return WarpPolicy{a ? atoi(a) : 8, b ? atoi(b) : 16};
     }();
+    return v;
+}
+bool use_wide() {   // 4-wide nodes for K5/K8 (scenes without an any-hit predicate); B2PT_BVH4=0: binary nodes
+    static const bool v = [] { const char* e = getenv("B2PT_BVH4"); return !(e && e[0] == '0'); }();
     return v;
 }
 bool use_deferred() {   // B2PT_DEFER=0: fp64 tests inside K5 (trace_persistent), for A/B measurements
@@ -201,10 +236,30 @@ bool use_persistent() {
 
 int trace_grid_blocks_per_sm() { return occ_blocks() > 0 ? occ_blocks() : 8; }
 
+int trace_node_bytes(const DeviceScene& sc) {
+    return use_persistent() && use_wide() && sc.any_alpha_texture == 0 ? (int)sizeof(BvhNode4) : (int)sizeof(BvhNode2);
+}
+
 void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState& st,
                     const uint32_t* n_active, float tmin, float tmax, HitRecord* hits,
                     TraceCounters* counters, bool finish) {
     const bool alpha = sc.any_alpha_texture != 0;
+    if (use_persistent() && use_wide() && !alpha) {
+        if (lc.stats)
+            k_closest_w<true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (occ_blocks() == 8)
+            k_closest_w<false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (occ_blocks() == 6)
+            k_closest_w<false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else
+            k_closest_w<false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        if (lc.launch_counter) ++*lc.launch_counter;
+        if (finish) {
+            k_finish_hits<<<lc.grid, 256, 0, lc.stream>>>(sc, st, n_active, hits);
+            if (lc.launch_counter) ++*lc.launch_counter;
+        }
+        return;
+    }
     if (use_persistent() && use_deferred() && !alpha) {
         if (lc.stats)
             k_closest_d<true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
@@ -254,6 +309,18 @@ void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh
                 const uint32_t* n_active, float tmin, uint32_t* info, uint8_t* occluded,
                 TraceCounters* counters) {
     const bool alpha = sc.any_alpha_texture != 0;
+    if (use_persistent() && use_wide() && !alpha) {
+        if (lc.stats)
+            k_any_w<true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (occ_blocks() == 8)
+            k_any_w<false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (occ_blocks() == 6)
+            k_any_w<false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else
+            k_any_w<false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        if (lc.launch_counter) ++*lc.launch_counter;
+        return;
+    }
     if (use_persistent()) {
         if (lc.stats && alpha)
             k_any_p<true, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());

@@ -71,6 +71,8 @@ struct LaunchCfg {
 
 // resident traversal blocks per SM the launchers size their grids for (B2PT_OCC overrides)
 int trace_grid_blocks_per_sm();
+// bytes of the node record K5/K8 read for this scene (64: binary nodes, 128: 4-wide nodes)
+int trace_node_bytes(const DeviceScene& sc);
 
 // K5: closest hit for rays [0, *n_active) of `st`; n_active lives on the device.
 void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState& st,
