@@ -277,8 +277,10 @@ int b2pt_bsdf_pdf(int32_t device, int32_t bsdf, int64_t n,
                   int32_t reflection, int32_t transmission, float* pdf_out);
 
 /* Read back the built acceleration structure (tests: structural checks).   *
- * nodes: n_nodes * node_bytes raw bytes; tri_order: n_triangles global
- * triangle ids in leaf order.  Either pointer may be NULL.                 */
+ * nodes: n_nodes * 64 raw bytes, the binary nodes the builder emits (the   *
+ * 4-wide nodes the traversal walks, node_bytes = 128, are derived from      *
+ * them); tri_order: n_triangles global triangle ids in leaf order.  Either  *
+ * pointer may be NULL.                                                      */
 int b2pt_download_bvh(B2ptRenderer* r, void* nodes, int32_t* tri_order);
 
 #ifdef __cplusplus

@@ -257,7 +257,8 @@ class OptixRenderer:
 
     def DownloadBvh(self):
         st = self.Stats()
-        nodes = np.empty((st["n_nodes"], st["node_bytes"] // 4), dtype=f32)
+        # the binary (64-byte) nodes the builder emits; the 4-wide nodes K5/K8 walk are derived from them
+        nodes = np.empty((st["n_nodes"], 16), dtype=f32)
         order = np.empty(st["n_triangles"], dtype=np.int32)
         check(self._h, self.lib.b2pt_download_bvh(self._h, nodes.ctypes.data_as(C.c_void_p),
                                                   order.ctypes.data_as(_lib.c_int32_p)))

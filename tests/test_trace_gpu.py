@@ -51,6 +51,7 @@ def test_bvh_structure():
         visited = 0
         stack = [0]
         while stack:
+            assert visited < nt, "the child links do not form a tree"
             c = stack.pop()
             if c < 0:
                 seen[~c] += 1
