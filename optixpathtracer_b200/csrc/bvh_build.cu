@@ -14,6 +14,7 @@
 //   k_karras       Karras 2012 topology, one thread per internal node
 //   k_refit        bottom-up AABB refit with arrival counters
 //   k_emit_*       leaf-order triangle / normal / uv records and 64-byte nodes
+#include <cstdlib>
 #include <vector>
 
 #include "scene.cuh"
@@ -289,42 +290,82 @@ k_emit_nodes(int n, const float3* __restrict__ wv, const uint32_t* __restrict__ 
     nodes[i] = nd;
 }
 
-// ---- K3d: collapse two binary levels into one 4-wide node ---------------------------
+// A/B switch: B2PT_COLLAPSE=fixed opens both children of every node (two binary levels per wide node)
+static int collapse_greedy() {
+    static const int v = [] { const char* e = getenv("B2PT_COLLAPSE"); return !(e && e[0] == 'f') ? 1 : 0; }();
+    return v;
+}
+
+// ---- K3d: collapse binary nodes into 4-wide nodes ---------------------------------------
+// Wide node i describes the subtree of binary node i.  Its slots start as the two children of i; while
+// a slot is free, the internal slot with the largest surface area is replaced by its own two children
+// (the usual surface-area-greedy collapse).  greedy = 0 keeps the fixed two-level collapse: both
+// children are opened, whatever their size.  Either way every descent crosses at least one binary level
+// and pushes at most three entries (kWideStackSize, trace_wide.cuh).
+struct Slot4 {
+    float lx, hx, ly, hy, lz, hz;
+    int32_t child;
+};
+__device__ __forceinline__ Slot4 slot_of(const BvhNode2& nd, int s) {
+    const float4 xy = s ? nd.c1xy : nd.c0xy;
+    Slot4 r;
+    r.lx = xy.x; r.hx = xy.y; r.ly = xy.z; r.hy = xy.w;
+    r.lz = s ? nd.cz.z : nd.cz.x;
+    r.hz = s ? nd.cz.w : nd.cz.y;
+    r.child = s ? nd.child1 : nd.child0;
+    return r;
+}
+__device__ __forceinline__ float slot_area(const Slot4& b) {
+    const float dx = b.hx - b.lx, dy = b.hy - b.ly, dz = b.hz - b.lz;
+    return dx * dy + dy * dz + dz * dx;
+}
 __global__ void __launch_bounds__(kThreads)
-k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restrict__ wide) {
+k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restrict__ wide, int greedy) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_nodes) return;
     const BvhNode2 nd = nodes[i];
-    float lo[3][4], hi[3][4];
-    int32_t ch[4];
+    Slot4 sl[4];
     int k = 0;
-    auto put = [&](float lx, float hx, float ly, float hy, float lz, float hz, int32_t c) {
-        lo[0][k] = lx; hi[0][k] = hx; lo[1][k] = ly; hi[1][k] = hy; lo[2][k] = lz; hi[2][k] = hz;
-        ch[k] = c;
-        k++;
-    };
 #pragma unroll
     for (int s = 0; s < 2; s++) {
-        const int32_t c = s ? nd.child1 : nd.child0;
-        const float4 xy = s ? nd.c1xy : nd.c0xy;
-        const float lz = s ? nd.cz.z : nd.cz.x, hz = s ? nd.cz.w : nd.cz.y;
-        if (c < 0 || !(xy.x <= xy.y)) {            // a leaf (or the never-hit slot of a one-triangle scene) stays one slot
-            if (xy.x <= xy.y) put(xy.x, xy.y, xy.z, xy.w, lz, hz, c);
-        } else {                                    // an internal child contributes its two children
-            const BvhNode2 g = nodes[c];
-            put(g.c0xy.x, g.c0xy.y, g.c0xy.z, g.c0xy.w, g.cz.x, g.cz.y, g.child0);
-            put(g.c1xy.x, g.c1xy.y, g.c1xy.z, g.c1xy.w, g.cz.z, g.cz.w, g.child1);
+        const Slot4 b = slot_of(nd, s);
+        if (b.lx <= b.hx) sl[k++] = b;             // drops the never-hit slot of a one-triangle scene
+    }
+    if (greedy) {
+        while (k < 4) {
+            int pick = -1;
+            float best = -1.0f;
+            for (int j = 0; j < k; j++) {
+                if (sl[j].child < 0) continue;
+                const float a = slot_area(sl[j]);
+                if (a > best) { best = a; pick = j; }
+            }
+            if (pick < 0) break;
+            const BvhNode2 g = nodes[sl[pick].child];
+            sl[pick] = slot_of(g, 0);
+            sl[k++] = slot_of(g, 1);
+        }
+    } else {
+        const int k0 = k;
+        for (int j = 0; j < k0; j++) {
+            if (sl[j].child < 0) continue;
+            const BvhNode2 g = nodes[sl[j].child];
+            sl[j] = slot_of(g, 0);
+            sl[k++] = slot_of(g, 1);
         }
     }
     // empty slot: lo = hi = +inf fails the slab test for every direction (an INVERTED box would pass it:
     // min(+inf, -inf) = -inf <= max = +inf)
-    for (; k < 4;) put(INFINITY, INFINITY, INFINITY, INFINITY, INFINITY, INFINITY, kEmptyChild);
+    for (; k < 4; k++) {
+        sl[k].lx = sl[k].hx = sl[k].ly = sl[k].hy = sl[k].lz = sl[k].hz = INFINITY;
+        sl[k].child = kEmptyChild;
+    }
     BvhNode4 w;
-    w.lox = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]); w.hix = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
-    w.loy = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]); w.hiy = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]);
-    w.loz = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]); w.hiz = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
+    w.lox = make_float4(sl[0].lx, sl[1].lx, sl[2].lx, sl[3].lx); w.hix = make_float4(sl[0].hx, sl[1].hx, sl[2].hx, sl[3].hx);
+    w.loy = make_float4(sl[0].ly, sl[1].ly, sl[2].ly, sl[3].ly); w.hiy = make_float4(sl[0].hy, sl[1].hy, sl[2].hy, sl[3].hy);
+    w.loz = make_float4(sl[0].lz, sl[1].lz, sl[2].lz, sl[3].lz); w.hiz = make_float4(sl[0].hz, sl[1].hz, sl[2].hz, sl[3].hz);
 #pragma unroll
-    for (int j = 0; j < 4; j++) { w.child[j] = ch[j]; w.pad[j] = 0; }
+    for (int j = 0; j < 4; j++) { w.child[j] = sl[j].child; w.pad[j] = 0; }
     wide[i] = w;
 }
 
@@ -601,7 +642,7 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
         k_emit_single<<<1, 1, 0, stream>>>(d_wv.get(), pad, out.nodes.get());
     }
     if (out.n_nodes > 0)
-        k_collapse4<<<blocks_for(out.n_nodes), kThreads, 0, stream>>>(out.n_nodes, out.nodes.get(), out.nodes4.get());
+        k_collapse4<<<blocks_for(out.n_nodes), kThreads, 0, stream>>>(out.n_nodes, out.nodes.get(), out.nodes4.get(), collapse_greedy());
     k_emit_tris<<<blocks_for(n), kThreads, 0, stream>>>(n, d_wv.get(), d_nrm.get(), order, d_tri_mesh.get(),
                                                          d_infos.get(), d_idx.get(), d_uv.get(),
                                                          out.tris.get(), out.nrms.get(), out.uvs.get());

@@ -11,7 +11,9 @@
 
 namespace b2pt {
 
-constexpr int kWideStackSize = kStackSize + kStackSize / 2;
+// a descent crosses at least one binary level (the greedy collapse, K3d, may open only one side) and
+// pushes at most three entries; the binary tree is at most kStackSize levels deep
+constexpr int kWideStackSize = 3 * kStackSize;
 
 // slab test of slot k of a wide node (same arithmetic as slab(), traverse.cuh)
 #define B2PT_SLAB4(k, comp)                                                                                   \
@@ -49,7 +51,6 @@ __device__ __forceinline__ void trace_wide(const BvhNode4* __restrict__ nodes, c
     c.lo = 0.0f;
     c.hi = 0.0f;
     __shared__ int s_stack[kSharedStack][kTraceBlock];
-    // up to three pushes per visit and a visit spans two binary levels: 1.5 entries per binary level
     int deep_stack[kWideStackSize - kSharedStack];
     int sp = 0;
     const int tid = threadIdx.x;
