@@ -7,8 +7,8 @@
 Metric (BASELINE.json): Msamples/s — complete camera paths per second, whole job
 over all N GPUs.  Workload at N=1: BASELINE.json configs[1] (README "Conductor"
 scene, 1024x1024, depth 16, 256 spp); a STEP is one pass of the hot path over
-one batch = `spp_per_step` samples of every pixel (default 16, so 16 steps are
-the whole 256-spp config).  Multi-GPU = weak scaling: every rank renders its
+one batch = `spp_per_step` samples of every pixel (default 64, so 4 steps are
+the whole 256-spp config; one step is ONE wave of 2^26 paths, 16 GB of wave state).  Multi-GPU = weak scaling: every rank renders its
 own spp_per_step samples per step (disjoint absolute sample indices, replicated
 scene/BVH) and the fp32 sums are combined with one NCCL reduce per step.
 
@@ -356,7 +356,7 @@ def run_b2pt(args, cfg):
             "config": {"workload": label, "config_id": args.config, "width": w, "height": h, "spp_per_step_per_gpu": spp,
                        "spp_config": spp_total, "max_depth": depth, "bsdf_mode": mode, "rng": "philox",
                        "triangles": st["n_triangles"], "bvh_nodes": st["n_nodes"], "bvh_build_ms": build_ms,
-                       "scene_device_bytes": st["scene_device_bytes"], "wave_paths_log2": args.wave_log2 or 22,
+                       "scene_device_bytes": st["scene_device_bytes"], "wave_paths_log2": args.wave_log2 or "auto (one wave per step, <= 2^26 paths)",
                        "parallelism": f"spp-split x{n_gpus}, replicated BVH, one NCCL reduce per step" if n_gpus > 1 else "single GPU",
                        "l2": "path state of a wave (~1 GB SoA) exceeds L2; the 16 MB BVH is L2-resident by nature of the workload"},
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
@@ -398,11 +398,11 @@ def main():
     guard_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b2pt", choices=["b2pt", "reference"])
     ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
-    ap.add_argument("--spp-per-step", type=int, default=16)
+    ap.add_argument("--spp-per-step", type=int, default=64)
     ap.add_argument("--wave-log2", type=int, default=0)
     ap.add_argument("--cpu-seconds", type=float, default=None, help="CPU work per reference step / baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -109,6 +109,7 @@ __device__ __forceinline__ void trace_closest_deferred(const BvhNode2* __restric
     const uint32_t lanes_lt = (1u << lane) - 1u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t chunk_sh = ray_chunk_shift(n_rays, n_warps, pol);
     uint32_t seq = 0;
 
     int node = kStackSentinel;
@@ -137,13 +138,13 @@ __device__ __forceinline__ void trace_closest_deferred(const BvhNode2* __restric
             has_ray = false;
         }
         const uint32_t idle_mask = __ballot_sync(kFullMask, idle);
-        const uint32_t chunk_first = ((seq / kRayChunk) * n_warps + warp) * kRayChunk;
+        const uint32_t chunk_first = (((seq >> chunk_sh) * n_warps + warp) << chunk_sh);
         const bool exhausted = chunk_first >= n_rays;
         if (exhausted && idle_mask == kFullMask) break;
         if (!exhausted && (int)__popc(idle_mask) >= kRefill) {
             if (idle) {
                 const uint32_t q = seq + (uint32_t)__popc(idle_mask & lanes_lt);
-                const uint32_t i = ((q / kRayChunk) * n_warps + warp) * kRayChunk + (q % kRayChunk);
+                const uint32_t i = ((((q >> chunk_sh) * n_warps + warp) << chunk_sh)) + (q & ((1u << chunk_sh) - 1u));
                 float3 o, d;
                 float tmax;
                 if (i < n_rays && n_nodes > 0 && io.load(i, o, d, tmax)) {

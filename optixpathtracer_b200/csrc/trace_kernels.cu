@@ -8,7 +8,7 @@
 #include "wavefront.cuh"
 #include "traverse.cuh"
 #include "alpha.cuh"
-#include "trace_wide.cuh"
+#include "trace_wideq.cuh"
 
 #include <cstdlib>
 
@@ -126,13 +126,16 @@ k_closest_d(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active,
 }
 
 // K5 / K8 over the 4-wide nodes (trace_wide.cuh)
-template <bool STATS, int MINB = 4>
+template <bool STATS, int MINB = 4, bool Q = false>
 __global__ void __launch_bounds__(kTraceThreads, MINB)
 k_closest_w(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active, float tmin, float tmax,
             HitRecord* __restrict__ hits, TraceCounters* counters, WarpPolicy pol) {
     TraceStats ts = {0, 0, 0, 0, 0};
     const ClosestIo io{st, hits, tmax};
-    trace_wide<false, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
+    if constexpr (Q)
+        trace_wideq<false, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
+    else
+        trace_wide<false, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
     if (STATS) {
         atomicAdd(&counters->nodes, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris, (unsigned long long)ts.tris);
@@ -141,13 +144,16 @@ k_closest_w(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active,
         atomicAdd(&counters->tri_slots, (unsigned long long)ts.tri_slots);
     }
 }
-template <bool STATS, int MINB = 4>
+template <bool STATS, int MINB = 4, bool Q = false>
 __global__ void __launch_bounds__(kTraceThreads, MINB)
 k_any_w(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, float tmin, uint32_t* info,
         uint8_t* occluded, TraceCounters* counters, WarpPolicy pol) {
     TraceStats ts = {0, 0, 0, 0, 0};
     const AnyIo io{sh, info, occluded};
-    trace_wide<true, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
+    if constexpr (Q)
+        trace_wideq<true, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
+    else
+        trace_wide<true, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
     if (STATS) {
         atomicAdd(&counters->nodes_any, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris_any, (unsigned long long)ts.tris);
@@ -215,12 +221,21 @@ WarpPolicy warp_policy() {
     static const WarpPolicy v = [] {
         const char* a = getenv("B2PT_REFILL");
         const char* b = getenv("B2PT_BREAK");
-        return WarpPolicy{a ? atoi(a) : 8, b ? atoi(b) : 16};
+        const char* q = getenv("B2PT_QBREAK");
+        const char* o = getenv("B2PT_QOUT");
+        int q_out = o ? atoi(o) : 1;
+        q_out = q_out < 1 ? 1 : (q_out > kQMaxOut - 1 ? kQMaxOut - 1 : q_out);
+        const char* sc = getenv("B2PT_SMALL_CHUNKS");
+        return WarpPolicy{a ? atoi(a) : 8, b ? atoi(b) : 16, q ? atoi(q) : 32, q_out, sc ? atoi(sc) : 1};
     }();
     return v;
 }
 bool use_wide() {   // 4-wide nodes for K5/K8 (scenes without an any-hit predicate); B2PT_BVH4=0: binary nodes
     static const bool v = [] { const char* e = getenv("B2PT_BVH4"); return !(e && e[0] == '0'); }();
+    return v;
+}
+bool use_triq() {   // B2PT_TRIQ=1: warp-shared triangle queue (trace_wideq.cuh) — bit-exact, measured 2-5 % slower, kept for A/B
+    static const bool v = [] { const char* e = getenv("B2PT_TRIQ"); return e && e[0] == '1'; }();
     return v;
 }
 bool use_deferred() {   // B2PT_DEFER=0: fp64 tests inside K5 (trace_persistent), for A/B measurements
@@ -245,7 +260,16 @@ void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState&
                     TraceCounters* counters, bool finish) {
     const bool alpha = sc.any_alpha_texture != 0;
     if (use_persistent() && use_wide() && !alpha) {
-        if (lc.stats)
+        const bool tq = use_triq() && sc.n_tris < kQSlotLimit;
+        if (lc.stats && tq)
+            k_closest_w<true, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (tq && occ_blocks() == 8)
+            k_closest_w<false, 8, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (tq && occ_blocks() == 6)
+            k_closest_w<false, 6, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (tq)
+            k_closest_w<false, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (lc.stats)
             k_closest_w<true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (occ_blocks() == 8)
             k_closest_w<false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
@@ -310,7 +334,16 @@ void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh
                 TraceCounters* counters) {
     const bool alpha = sc.any_alpha_texture != 0;
     if (use_persistent() && use_wide() && !alpha) {
-        if (lc.stats)
+        const bool tq = use_triq() && sc.n_tris < kQSlotLimit;
+        if (lc.stats && tq)
+            k_any_w<true, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (tq && occ_blocks() == 8)
+            k_any_w<false, 8, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (tq && occ_blocks() == 6)
+            k_any_w<false, 6, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (tq)
+            k_any_w<false, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (lc.stats)
             k_any_w<true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (occ_blocks() == 8)
             k_any_w<false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());

@@ -64,7 +64,7 @@ __device__ __forceinline__ int tri_classify(float3 o, float3 d, float d_l1, floa
 }
 
 constexpr uint32_t kFullMask = 0xffffffffu;
-constexpr uint32_t kRayChunk = 64;
+constexpr uint32_t kRayChunkShift = 6;   // a warp takes its rays in chunks of 64 ...
 constexpr int kSharedStack = 16;   // stack levels kept in shared memory
 constexpr int kTraceBlock = 128;   // threads per block of the traversal kernels
 
@@ -73,7 +73,21 @@ constexpr int kTraceBlock = 128;   // threads per block of the traversal kernels
 struct WarpPolicy {
     int refill_lanes;   // take new rays when this many lanes are idle
     int break_lanes;    // leave the descent when this many lanes cannot descend (hold two leaves / are done)
+    int q_break;        // trace_wideq: ... or when the warp's triangle queue holds this many entries
+    int q_out;          // trace_wideq: leaves a lane may queue and keep descending (1 or 2)
+    int small_chunks;   // 1: launches with fewer than 64 rays per warp use smaller chunks (ray_chunk_shift)
 };
+
+// ... unless the launch is small.  The late bounces of a wave hold a few thousand rays (c2: 0.06 % of the paths
+// reach bounce 16); in 64-ray chunks they would queue behind each other in a handful of warps while the
+// other 3 500 warps of the grid exit at once, and the launch lasts 2-3 ray lifetimes of a lone warp
+// (~120 us measured, whatever the ray count).  With fewer than 64 rays per warp the chunk shrinks to the
+// largest power of two <= rays / warps, down to one ray per warp: every ray starts at once.
+__device__ __forceinline__ uint32_t ray_chunk_shift(uint32_t n_rays, uint32_t n_warps, const WarpPolicy& pol) {
+    const uint32_t per = n_rays / n_warps;
+    if (!pol.small_chunks || per >= (1u << kRayChunkShift)) return kRayChunkShift;
+    return per <= 1u ? 0u : 31u - (uint32_t)__clz((int)per);
+}
 
 template <bool ANY, bool STATS, class Accept, class Io>
 __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ nodes,
@@ -85,6 +99,7 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
     const uint32_t lanes_lt = (1u << lane) - 1u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t chunk_sh = ray_chunk_shift(n_rays, n_warps, pol);
     uint32_t seq = 0;   // warp-uniform: next position of this warp's ray sequence
 
     // per-lane ray state
@@ -119,13 +134,13 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
             has_ray = false;
         }
         const uint32_t idle_mask = __ballot_sync(kFullMask, idle);
-        const uint32_t chunk_first = ((seq / kRayChunk) * n_warps + warp) * kRayChunk;
+        const uint32_t chunk_first = (((seq >> chunk_sh) * n_warps + warp) << chunk_sh);
         const bool exhausted = chunk_first >= n_rays;   // chunks only grow: nothing left for this warp
         if (exhausted && idle_mask == kFullMask) break;
         if (!exhausted && (int)__popc(idle_mask) >= kRefill) {
             if (idle) {
                 const uint32_t q = seq + (uint32_t)__popc(idle_mask & lanes_lt);
-                const uint32_t i = ((q / kRayChunk) * n_warps + warp) * kRayChunk + (q % kRayChunk);
+                const uint32_t i = ((((q >> chunk_sh) * n_warps + warp) << chunk_sh)) + (q & ((1u << chunk_sh) - 1u));
                 float3 o, d;
                 float tmax;
                 if (i < n_rays && n_nodes > 0 && io.load(i, o, d, tmax)) {

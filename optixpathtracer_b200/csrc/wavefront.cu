@@ -421,7 +421,23 @@ void render_frames(B2ptRenderer* r, int spp, bool accumulate) {
     B2PT_REQUIRE(accumulate || spp == 1, B2PT_E_INVALID, "Render traces exactly one sample per pixel");
     const uint64_t n_pixels = (uint64_t)r->width * r->height;
     int log2cap = r->cfg.wave_paths_log2;
-    if (log2cap <= 0) log2cap = 22;
+    if (log2cap <= 0) {
+        // Default: the whole call in ONE wave when it fits (up to 2^26 paths = 16 GB of wave state; a B200 has
+        // 180 GB).  The late bounces of a wave are latency-bound launches — a few thousand rays, each launch
+        // lasting as long as its slowest ray, ~0.1 ms whatever the count (profiles/r01_launches_wide.csv) — so
+        // their cost is per WAVE, not per path: c2 374 -> 452 -> 480 Msamples/s for 2^22 -> 2^24 -> 2^26.
+        // Grow-only: a later, smaller call (Render after RenderAccumulate) keeps the buffers.
+        const uint64_t want = n_pixels * (uint64_t)std::max(spp, 1);
+        log2cap = 20;
+        while ((1ull << log2cap) < want && log2cap < 26) log2cap++;
+        const size_t per_path = (size_t)(2 * kPathStateWords + kSurfaceStateWords + kShadowWords) * 4 + sizeof(HitRecord) + 16 + 12;
+        size_t free_b = 0, total_b = 0;
+        B2PT_CUDA(cudaMemGetInfo(&free_b, &total_b));
+        const size_t held = r->d_hits.size();                      // paths the buffers hold now
+        const size_t have = held * per_path;                       // released before a larger allocation
+        while (log2cap > 20 && (per_path << log2cap) > (free_b + have) / 2) log2cap--;
+        while (log2cap < 27 && ((size_t)1 << log2cap) < held) log2cap++;
+    }
     B2PT_REQUIRE(log2cap >= 10 && log2cap <= 27, B2PT_E_INVALID, "wave_paths_log2 must be in [10, 27]");
     const uint32_t capacity = 1u << log2cap;
     layout_wave(r, capacity);

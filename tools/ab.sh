@@ -5,6 +5,6 @@ for v in "$@"; do
   python - "$v" <<'PY'
 import json,sys
 d=json.load(open("gpurun_out/ab.json")); r=d["roofline"]
-print(sys.argv[1], "|", round(d["value"],1),"Msamples/s", round(d["mrays_per_s"]),"Mrays/s", {k:round(x,3) for k,x in r["share_of_step"].items()}, "closest ms/launch", round(r["ms_per_launch"],3), "frac", round(r["frac"],3))
+print(sys.argv[1], "|", round(d["value"],1),"Msamples/s", round(d["mrays_per_s"]),"Mrays/s", {k:round(x,3) for k,x in r["share_of_step"].items()}, "closest ms/launch", round(r["ms_per_launch"],3), "frac", round(r["frac"],3), "nodes/ray", round(r["nodes_per_ray"],2), "tris/ray", round(r["tris_per_ray"],2), "simd", round(r["simd_node_loop"],3), round(r["simd_tri_loop"],3))
 PY
 done
