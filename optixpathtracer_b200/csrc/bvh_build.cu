@@ -319,8 +319,56 @@ __device__ __forceinline__ float slot_area(const Slot4& b) {
     const float dx = b.hx - b.lx, dy = b.hy - b.ly, dz = b.hz - b.lz;
     return dx * dy + dy * dz + dz * dx;
 }
+// One axis of BvhNode4Q: origin o = lowest low plane, scale 2^(e-127) = the smallest power of two with
+// (highest high plane - o) <= 255 steps, planes rounded outward.  fp32 differences and power-of-two
+// divisions are exact in double, so floor / ceil act on the real values.
+__device__ __forceinline__ void quantise_axis(const float lo[4], const float hi[4], const bool used[4], float& o,
+                                              uint32_t& e, uint32_t& qlo, uint32_t& qhi) {
+    float omin = INFINITY, hmax = -INFINITY;
+    for (int k = 0; k < 4; k++)
+        if (used[k]) { omin = fminf(omin, lo[k]); hmax = fmaxf(hmax, hi[k]); }
+    o = omin;
+    const double ext = (double)hmax - (double)omin;
+    int eb = 1;                                            // biased exponent; 2^-126 for a flat axis
+    if (ext > 0.0) {
+        int ex;
+        frexp(ext / 255.0, &ex);                           // ext / 255 = m * 2^ex, m in [0.5, 1)  ->  2^ex >= ext / 255
+        eb = ex + 127;
+        eb = eb < 1 ? 1 : eb;
+    }
+    const double step = ldexp(1.0, eb - 127);
+    e = (uint32_t)eb;
+    qlo = qhi = 0u;
+    for (int k = 0; k < 4; k++) {
+        if (!used[k]) continue;
+        double a = floor(((double)lo[k] - (double)omin) / step);
+        double b = ceil(((double)hi[k] - (double)omin) / step);
+        a = a < 0.0 ? 0.0 : a;
+        b = b > 255.0 ? 255.0 : b;                         // cannot exceed: ext / step <= 255
+        qlo |= (uint32_t)a << (8 * k);
+        qhi |= (uint32_t)b << (8 * k);
+    }
+}
+__device__ __forceinline__ BvhNode4Q quantise4(const Slot4 sl[4]) {
+    bool used[4];
+    float lo[4], hi[4];
+    BvhNode4Q q;
+    uint32_t ex, ey, ez;
+    for (int k = 0; k < 4; k++) { used[k] = sl[k].child != kEmptyChild; q.child[k] = sl[k].child; }
+    for (int k = 0; k < 4; k++) { lo[k] = sl[k].lx; hi[k] = sl[k].hx; }
+    quantise_axis(lo, hi, used, q.ox, ex, q.qlox, q.qhix);
+    for (int k = 0; k < 4; k++) { lo[k] = sl[k].ly; hi[k] = sl[k].hy; }
+    quantise_axis(lo, hi, used, q.oy, ey, q.qloy, q.qhiy);
+    for (int k = 0; k < 4; k++) { lo[k] = sl[k].lz; hi[k] = sl[k].hz; }
+    quantise_axis(lo, hi, used, q.oz, ez, q.qloz, q.qhiz);
+    q.exps = ex | (ey << 8) | (ez << 16);
+    q.pad0 = q.pad1 = 0u;
+    return q;
+}
+
 __global__ void __launch_bounds__(kThreads)
-k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restrict__ wide, int greedy) {
+k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restrict__ wide, BvhNode4Q* __restrict__ wideq,
+            int greedy) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_nodes) return;
     const BvhNode2 nd = nodes[i];
@@ -360,6 +408,7 @@ k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restric
         sl[k].lx = sl[k].hx = sl[k].ly = sl[k].hy = sl[k].lz = sl[k].hz = INFINITY;
         sl[k].child = kEmptyChild;
     }
+    if (wideq) wideq[i] = quantise4(sl);
     BvhNode4 w;
     w.lox = make_float4(sl[0].lx, sl[1].lx, sl[2].lx, sl[3].lx); w.hix = make_float4(sl[0].hx, sl[1].hx, sl[2].hx, sl[3].hx);
     w.loy = make_float4(sl[0].ly, sl[1].ly, sl[2].ly, sl[3].ly); w.hiy = make_float4(sl[0].hy, sl[1].hy, sl[2].hy, sl[3].hy);
@@ -425,6 +474,7 @@ DeviceScene SceneBuffers::view() const {
     DeviceScene s;
     s.nodes = nodes.get();
     s.nodes4 = nodes4.get();
+    s.nodes4q = nodes4q.get();
     s.tris = tris.get();
     s.nrms = nrms.get();
     s.uvs = uvs.get();
@@ -435,11 +485,13 @@ DeviceScene SceneBuffers::view() const {
     s.n_meshes = n_meshes;
     s.n_textures = n_textures;
     s.any_alpha_texture = any_alpha_texture;
+    s.max_abs = fmaxf(fmaxf(fmaxf(fabsf(bounds_lo.x), fabsf(bounds_lo.y)), fabsf(bounds_lo.z)),
+                      fmaxf(fmaxf(fabsf(bounds_hi.x), fabsf(bounds_hi.y)), fabsf(bounds_hi.z)));
     return s;
 }
 
 int64_t SceneBuffers::device_bytes() const {
-    return (int64_t)(nodes.bytes() + nodes4.bytes() + tris.bytes() + nrms.bytes() + uvs.bytes() + materials.bytes() +
+    return (int64_t)(nodes.bytes() + nodes4.bytes() + nodes4q.bytes() + tris.bytes() + nrms.bytes() + uvs.bytes() + materials.bytes() +
                      textures.bytes() + tri_order.bytes());
 }
 
@@ -554,6 +606,7 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
     out.n_nodes = n == 0 ? 0 : (n == 1 ? 1 : n - 1);
     out.nodes.alloc((size_t)out.n_nodes);
     out.nodes4.alloc((size_t)out.n_nodes);
+    out.nodes4q.alloc((size_t)out.n_nodes);
     out.tris.alloc((size_t)n);
     out.nrms.alloc((size_t)n);
     out.uvs.alloc(any_uv ? (size_t)n : 0);
@@ -611,8 +664,8 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
         maxabs = fmaxf(maxabs, fabsf(ord2f(hb.vhi[i])));
     }
     B2PT_REQUIRE(std::isfinite(maxabs), B2PT_E_INVALID, "non-finite vertex positions");
-    // outward box padding: 2^-18 of the largest coordinate (see traverse.cuh)
-    const float pad = fmaxf(maxabs, 1e-30f) * 3.8146973e-6f;
+    // outward box padding: 2^-17 of the largest coordinate (see traverse.cuh, trace_wide.cuh)
+    const float pad = fmaxf(maxabs, 1e-30f) * 7.6293945e-6f;
 
     k_morton<<<blocks_for(n), kThreads, 0, stream>>>(n, d_wv.get(), d_bounds.get(), d_keys[0].get(),
                                                       d_vals[0].get());
@@ -642,7 +695,7 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
         k_emit_single<<<1, 1, 0, stream>>>(d_wv.get(), pad, out.nodes.get());
     }
     if (out.n_nodes > 0)
-        k_collapse4<<<blocks_for(out.n_nodes), kThreads, 0, stream>>>(out.n_nodes, out.nodes.get(), out.nodes4.get(), collapse_greedy());
+        k_collapse4<<<blocks_for(out.n_nodes), kThreads, 0, stream>>>(out.n_nodes, out.nodes.get(), out.nodes4.get(), out.nodes4q.get(), collapse_greedy());
     k_emit_tris<<<blocks_for(n), kThreads, 0, stream>>>(n, d_wv.get(), d_nrm.get(), order, d_tri_mesh.get(),
                                                          d_infos.get(), d_idx.get(), d_uv.get(),
                                                          out.tris.get(), out.nrms.get(), out.uvs.get());

@@ -44,6 +44,7 @@ struct MeshInfo {
 struct DeviceScene {
     const BvhNode2* nodes;
     const BvhNode4* nodes4;         // the same tree, two levels per node (bvh.cuh)
+    const BvhNode4Q* nodes4q;       // ... and those in 64 bytes, child boxes quantised (what K5/K8 read)
     const TriRecord* tris;
     const NrmRecord* nrms;
     const UvRecord* uvs;            // nullptr when no mesh has texcoords
@@ -54,11 +55,13 @@ struct DeviceScene {
     int32_t n_meshes;
     int32_t n_textures;
     int32_t any_alpha_texture;      // some mesh has an albedo texture (any-hit cut-out, A9)
+    float max_abs;                  // largest |coordinate| of the geometry (the boxes are padded by 2^-18 of it)
 };
 
 struct SceneBuffers {
     DeviceBuffer<BvhNode2> nodes;
     DeviceBuffer<BvhNode4> nodes4;
+    DeviceBuffer<BvhNode4Q> nodes4q;
     DeviceBuffer<TriRecord> tris;
     DeviceBuffer<NrmRecord> nrms;
     DeviceBuffer<UvRecord> uvs;

@@ -126,7 +126,7 @@ k_closest_d(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active,
 }
 
 // K5 / K8 over the 4-wide nodes (trace_wide.cuh)
-template <bool STATS, int MINB = 4, bool Q = false>
+template <bool STATS, int MINB = 4, bool Q = false, int STEP = 0>
 __global__ void __launch_bounds__(kTraceThreads, MINB)
 k_closest_w(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active, float tmin, float tmax,
             HitRecord* __restrict__ hits, TraceCounters* counters, WarpPolicy pol) {
@@ -135,7 +135,7 @@ k_closest_w(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active,
     if constexpr (Q)
         trace_wideq<false, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
     else
-        trace_wide<false, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
+        trace_wide<false, STATS, STEP>(STEP == 2 ? (const void*)sc.nodes4q : (const void*)sc.nodes4, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io, ts, pol);
     if (STATS) {
         atomicAdd(&counters->nodes, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris, (unsigned long long)ts.tris);
@@ -144,7 +144,7 @@ k_closest_w(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active,
         atomicAdd(&counters->tri_slots, (unsigned long long)ts.tri_slots);
     }
 }
-template <bool STATS, int MINB = 4, bool Q = false>
+template <bool STATS, int MINB = 4, bool Q = false, int STEP = 0>
 __global__ void __launch_bounds__(kTraceThreads, MINB)
 k_any_w(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, float tmin, uint32_t* info,
         uint8_t* occluded, TraceCounters* counters, WarpPolicy pol) {
@@ -153,7 +153,7 @@ k_any_w(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, fl
     if constexpr (Q)
         trace_wideq<true, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
     else
-        trace_wide<true, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
+        trace_wide<true, STATS, STEP>(STEP == 2 ? (const void*)sc.nodes4q : (const void*)sc.nodes4, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io, ts, pol);
     if (STATS) {
         atomicAdd(&counters->nodes_any, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris_any, (unsigned long long)ts.tris);
@@ -234,6 +234,13 @@ bool use_wide() {   // 4-wide nodes for K5/K8 (scenes without an any-hit predica
     static const bool v = [] { const char* e = getenv("B2PT_BVH4"); return !(e && e[0] == '0'); }();
     return v;
 }
+// B2PT_STEP selects the node step of trace_wide (all bit-exact, A/B in profiles/r01_ab_node_step.txt):
+// 4 = fp32 nodes, FMA-form slabs, four 256-bit loads (default); 3 = warp-cooperative cp.async fetch (slower);
+// 2 = 64-byte quantised nodes (issue-bound, slower); 1 = FMA-form slabs, seven 128-bit loads; 0 = the first step
+int node_step() {
+    static const int v = [] { const char* e = getenv("B2PT_STEP"); return e ? atoi(e) : 4; }();
+    return v;
+}
 bool use_triq() {   // B2PT_TRIQ=1: warp-shared triangle queue (trace_wideq.cuh) — bit-exact, measured 2-5 % slower, kept for A/B
     static const bool v = [] { const char* e = getenv("B2PT_TRIQ"); return e && e[0] == '1'; }();
     return v;
@@ -252,7 +259,9 @@ bool use_persistent() {
 int trace_grid_blocks_per_sm() { return occ_blocks() > 0 ? occ_blocks() : 8; }
 
 int trace_node_bytes(const DeviceScene& sc) {
-    return use_persistent() && use_wide() && sc.any_alpha_texture == 0 ? (int)sizeof(BvhNode4) : (int)sizeof(BvhNode2);
+    if (use_persistent() && use_wide() && sc.any_alpha_texture == 0)
+        return node_step() == 2 && !use_triq() ? (int)sizeof(BvhNode4Q) : (int)sizeof(BvhNode4);
+    return (int)sizeof(BvhNode2);
 }
 
 void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState& st,
@@ -269,6 +278,30 @@ void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState&
             k_closest_w<false, 6, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (tq)
             k_closest_w<false, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (lc.stats && node_step() == 4)
+            k_closest_w<true, 4, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 4 && occ_blocks() == 6)
+            k_closest_w<false, 6, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 4 && occ_blocks() == 8)
+            k_closest_w<false, 8, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (lc.stats && node_step() == 3)
+            k_closest_w<true, 4, false, 3><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 3 && occ_blocks() == 6)
+            k_closest_w<false, 6, false, 3><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 3 && occ_blocks() == 8)
+            k_closest_w<false, 8, false, 3><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (lc.stats && node_step() == 2)
+            k_closest_w<true, 4, false, 2><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 2 && occ_blocks() == 6)
+            k_closest_w<false, 6, false, 2><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 2 && occ_blocks() == 8)
+            k_closest_w<false, 8, false, 2><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (lc.stats && node_step() == 1)
+            k_closest_w<true, 4, false, 1><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 1 && occ_blocks() == 6)
+            k_closest_w<false, 6, false, 1><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 1 && occ_blocks() == 8)
+            k_closest_w<false, 8, false, 1><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (lc.stats)
             k_closest_w<true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (occ_blocks() == 8)
@@ -343,6 +376,30 @@ void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh
             k_any_w<false, 6, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (tq)
             k_any_w<false, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (lc.stats && node_step() == 4)
+            k_any_w<true, 4, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 4 && occ_blocks() == 6)
+            k_any_w<false, 6, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 4 && occ_blocks() == 8)
+            k_any_w<false, 8, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (lc.stats && node_step() == 3)
+            k_any_w<true, 4, false, 3><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 3 && occ_blocks() == 6)
+            k_any_w<false, 6, false, 3><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 3 && occ_blocks() == 8)
+            k_any_w<false, 8, false, 3><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (lc.stats && node_step() == 2)
+            k_any_w<true, 4, false, 2><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 2 && occ_blocks() == 6)
+            k_any_w<false, 6, false, 2><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 2 && occ_blocks() == 8)
+            k_any_w<false, 8, false, 2><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (lc.stats && node_step() == 1)
+            k_any_w<true, 4, false, 1><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 1 && occ_blocks() == 6)
+            k_any_w<false, 6, false, 1><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 1 && occ_blocks() == 8)
+            k_any_w<false, 8, false, 1><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (lc.stats)
             k_any_w<true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (occ_blocks() == 8)
