@@ -53,8 +53,11 @@ def make_scene(spec):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (profiling recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+    """nvidia-smi clocks / throttle reasons DURING the timed region (profiling recipe).  The process is
+    started BEFORE the warm-up steps — its start-up (NVML attach) stalls kernel launches on the GPU for ~0.1 s,
+    which used to land inside short timed regions — and only the samples whose timestamps fall inside the timed
+    region (mark_begin .. stop) are used."""
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
@@ -73,7 +76,13 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def mark_begin(self):
+        self.t_begin = time.time()
+
     def stop(self) -> dict:
+        import datetime
+        t_end = time.time()
+        t_begin = getattr(self, "t_begin", 0.0)
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
         if self.proc is None:
             return out
@@ -82,19 +91,25 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = []   # (inside the timed region?, sm, max sm, reasons)
         for line in open(self.path).read().splitlines():
             c = [x.strip() for x in line.split(",")]
             if len(c) < 9:
                 continue
             try:
-                sm.append(float(c[1])); mx.append(float(c[2]))
+                sm_v, mx_v = float(c[1]), float(c[2])
             except ValueError:
                 continue
-            for n, v in zip(names, c[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
+            try:
+                ts = datetime.datetime.strptime(c[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                inside = t_begin - 0.25 <= ts <= t_end + 0.25   # one sampling period of slack either side
+            except ValueError:
+                inside = True
+            rows.append((inside, sm_v, mx_v, {n for n, v in zip(names, c[5:9]) if v.lower().startswith("active")}))
+        if any(r[0] for r in rows):
+            rows = [r for r in rows if r[0]]
+        sm, mx, reasons = [r[1] for r in rows], [r[2] for r in rows], set().union(*[r[3] for r in rows]) if rows else set()
         os.unlink(self.path)
         if sm:
             out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons), samples=len(sm))
@@ -246,15 +261,16 @@ def run_b2pt(args, cfg):
             total.add_(acc)
         torch.cuda.current_stream().synchronize()
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     for k in range(args.warmup):
         step(k, 1_000_000)
     total.zero_()
     r.ResetStats()
     r.SetKernelTiming(True)
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     barrier()
+    sampler.mark_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     e0.record()
@@ -325,7 +341,10 @@ def run_b2pt(args, cfg):
     tpath = ROOT / "profiles" / "traffic.json"
     if tpath.exists():
         try:
-            traffic = json.load(open(tpath)).get(args.config, {}).get("k_closest_dram_bytes_per_launch")
+            tj = json.load(open(tpath)).get(args.config, {})
+            traffic = tj.get("k_closest_dram_bytes_per_launch")
+            if traffic is None and tj.get("k_closest_dram_bytes_per_ray") is not None:   # per ray (ncu) x rays of the average launch
+                traffic = tj["k_closest_dram_bytes_per_ray"] * st["radiance_rays"] / max(n_k[0], 1)
         except Exception:
             traffic = None
     roofline = {"kernel": "k_closest (K5 closest-hit BVH traversal)", "bound": "hbm", "achieved": achieved, "peak": peak,
@@ -338,8 +357,9 @@ def run_b2pt(args, cfg):
                                   "shade": ms_k[3] / render_ms, "other": ms_k[4] / render_ms},
                 "shadow": {"achieved": st["shadow_rays_traced"] * bpr["any"] / (max(ms_k[1], 1e-9) * 1e-3) / 1e9,
                            "bytes_per_ray": bpr["any"]},
-                "note": "scene BVH+triangles are L2-resident for the README scenes (16 MB < 126 MB L2): the HBM fraction can "
-                        "exceed what DRAM traffic shows; see DESIGN.md"}
+                "note": "algorithmic bytes (nodes + triangles a ray must read) are served by L1/L2 — the README scenes' BVH is "
+                        "16 MB, L2 holds 126 MB — so frac can exceed 1; DRAM sees only the ray/hit I/O (`traffic`, ~40 B/ray). "
+                        "ncu: the kernel's limiter is the L1TEX data pipe (85 % busy), see DESIGN.md section 4"}
 
     cpu = None
     if n_gpus == 1 and not args.no_cpu_baseline:

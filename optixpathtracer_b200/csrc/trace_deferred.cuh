@@ -173,10 +173,9 @@ __device__ __forceinline__ void trace_closest_deferred(const BvhNode2* __restric
               if (node >= 0 && node != kStackSentinel) {
                 if (STATS) ts.nodes++;
                 const BvhNode2* np = nodes + node;
-                const float4 a = B2PT_LDG4(&np->c0xy);
-                const float4 b = B2PT_LDG4(&np->c1xy);
-                const float4 cz = B2PT_LDG4(&np->cz);
-                const float4 m = B2PT_LDG4(&np->child0);
+                float4 a, b, cz, m;
+                ldg256(&np->c0xy, a, b);
+                ldg256(&np->cz, cz, m);
                 float t0, t1;
                 const bool h0 = slab(r, a.x, a.y, a.z, a.w, cz.x, cz.y, tmin, c.hi, t0);
                 const bool h1 = slab(r, b.x, b.y, b.z, b.w, cz.z, cz.w, tmin, c.hi, t1);

@@ -235,10 +235,11 @@ bool use_wide() {   // 4-wide nodes for K5/K8 (scenes without an any-hit predica
     return v;
 }
 // B2PT_STEP selects the node step of trace_wide (all bit-exact, A/B in profiles/r01_ab_node_step.txt):
-// 4 = fp32 nodes, FMA-form slabs, four 256-bit loads (default); 3 = warp-cooperative cp.async fetch (slower);
+// 5 = fp32 nodes, FMA-form slabs, three 256-bit loads + one 128-bit load of the child indices (default);
+// 4 = four 256-bit loads (reads the 16 pad bytes too); 3 = warp-cooperative cp.async fetch (slower);
 // 2 = 64-byte quantised nodes (issue-bound, slower); 1 = FMA-form slabs, seven 128-bit loads; 0 = the first step
 int node_step() {
-    static const int v = [] { const char* e = getenv("B2PT_STEP"); return e ? atoi(e) : 4; }();
+    static const int v = [] { const char* e = getenv("B2PT_STEP"); return e ? atoi(e) : 5; }();
     return v;
 }
 bool use_triq() {   // B2PT_TRIQ=1: warp-shared triangle queue (trace_wideq.cuh) — bit-exact, measured 2-5 % slower, kept for A/B
@@ -278,6 +279,12 @@ void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState&
             k_closest_w<false, 6, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (tq)
             k_closest_w<false, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (lc.stats && node_step() == 5)
+            k_closest_w<true, 4, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 5 && occ_blocks() == 6)
+            k_closest_w<false, 6, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 5 && occ_blocks() == 8)
+            k_closest_w<false, 8, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (lc.stats && node_step() == 4)
             k_closest_w<true, 4, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (node_step() == 4 && occ_blocks() == 6)
@@ -376,6 +383,12 @@ void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh
             k_any_w<false, 6, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (tq)
             k_any_w<false, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (lc.stats && node_step() == 5)
+            k_any_w<true, 4, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 5 && occ_blocks() == 6)
+            k_any_w<false, 6, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 5 && occ_blocks() == 8)
+            k_any_w<false, 8, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (lc.stats && node_step() == 4)
             k_any_w<true, 4, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (node_step() == 4 && occ_blocks() == 6)

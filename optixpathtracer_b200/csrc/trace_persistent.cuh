@@ -63,6 +63,13 @@ __device__ __forceinline__ int tri_classify(float3 o, float3 d, float d_l1, floa
     return inside ? 2 : 1;
 }
 
+// 256-bit read-only load (sm_100: LDG.E.256): two float4 of a 32-byte-aligned record in ONE L1TEX wavefront
+__device__ __forceinline__ void ldg256(const void* p, float4& a, float4& b) {
+    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+        : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+        : "l"(p));
+}
+
 constexpr uint32_t kFullMask = 0xffffffffu;
 constexpr uint32_t kRayChunkShift = 6;   // a warp takes its rays in chunks of 64 ...
 constexpr int kSharedStack = 16;   // stack levels kept in shared memory
@@ -178,10 +185,9 @@ __device__ __forceinline__ void trace_persistent(const BvhNode2* __restrict__ no
               if (node >= 0 && node != kStackSentinel) {
                 if (STATS) ts.nodes++;
                 const BvhNode2* np = nodes + node;
-                const float4 a = B2PT_LDG4(&np->c0xy);
-                const float4 b = B2PT_LDG4(&np->c1xy);
-                const float4 c = B2PT_LDG4(&np->cz);
-                const float4 m = B2PT_LDG4(&np->child0);
+                float4 a, b, c, m;   // the 64-byte node as two 256-bit loads: half the L1TEX wavefronts
+                ldg256(&np->c0xy, a, b);
+                ldg256(&np->cz, c, m);
                 float t0, t1;
                 const bool h0 = slab(r, a.x, a.y, a.z, a.w, c.x, c.y, tmin, best32, t0);
                 const bool h1 = slab(r, b.x, b.y, b.z, b.w, c.z, c.w, tmin, best32, t1);

@@ -45,12 +45,6 @@ __device__ __forceinline__ void cp_async_16(void* smem_dst, const void* gmem_src
     const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
     asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gmem_src) : "memory");
 }
-// 256-bit read-only load (sm_100: LDG.E.256): two float4 of a 32-byte-aligned record in ONE L1TEX wavefront
-__device__ __forceinline__ void ldg256(const void* p, float4& a, float4& b) {
-    asm("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-        : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
-        : "l"(p));
-}
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
 
 // ANY = false: closest hit, deferred (Io::store_slot).  ANY = true: occlusion (Io::store(i, hit, occluded)).
@@ -60,7 +54,10 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // distances compare differently.
 // STEP = 2: DIET over the 64-byte quantised nodes (BvhNode4Q): 4 loads per visit instead of 7.
 // STEP = 4: DIET over the fp32 nodes read with four 256-bit loads (LDG.E.256, new on sm_100) instead of seven
-// 128-bit ones: the same 128 bytes in four L1TEX wavefronts per lane.
+// 128-bit ones.  STEP = 5 (default): three 256-bit loads for the boxes and one 128-bit load for the child
+// indices — the pad bytes of the node are not read.  ncu: a divergent 256-bit load is not free, the L1TEX
+// data pipe still moves it as more than one wavefront (8.3 M wavefronts per SM against 9.0 M for the 128-bit
+// form on the same launch), but the launch is 6-8 % shorter.
 // STEP = 3: DIET over the fp32 nodes, fetched by the warp TOGETHER.  A lane's seven 16-byte loads of its own
 // node cost seven L1TEX wavefronts — divergent lanes, one wavefront per lane per instruction, 16 of the
 // pipe's 128 bytes used; ncu of the fp32 step: L1TEX 88 % busy, long-scoreboard 5.1 of 10.6 cycles per
@@ -224,14 +221,19 @@ __device__ __forceinline__ void trace_wide(const void* __restrict__ nodes_v, con
                     const float4 chf = sn[6 ^ sw];
                     ch = make_int4(__float_as_int(chf.x), __float_as_int(chf.y), __float_as_int(chf.z), __float_as_int(chf.w));
                     B2PT_SLAB4F(0, x) B2PT_SLAB4F(1, y) B2PT_SLAB4F(2, z) B2PT_SLAB4F(3, w)
-                } else if constexpr (STEP == 4) {
+                } else if constexpr (STEP == 4 || STEP == 5) {
                     const BvhNode4* np = static_cast<const BvhNode4*>(nodes_v) + node;
-                    float4 lox, hix, loy, hiy, loz, hiz, chf, padf;
+                    float4 lox, hix, loy, hiy, loz, hiz;
                     ldg256(&np->lox, lox, hix);
                     ldg256(&np->loy, loy, hiy);
                     ldg256(&np->loz, loz, hiz);
-                    ldg256(np->child, chf, padf);
-                    ch = make_int4(__float_as_int(chf.x), __float_as_int(chf.y), __float_as_int(chf.z), __float_as_int(chf.w));
+                    if constexpr (STEP == 4) {
+                        float4 chf, padf;
+                        ldg256(np->child, chf, padf);
+                        ch = make_int4(__float_as_int(chf.x), __float_as_int(chf.y), __float_as_int(chf.z), __float_as_int(chf.w));
+                    } else {
+                        ch = __ldg(reinterpret_cast<const int4*>(np->child));
+                    }
                     B2PT_SLAB4F(0, x) B2PT_SLAB4F(1, y) B2PT_SLAB4F(2, z) B2PT_SLAB4F(3, w)
                 } else {
                     const BvhNode4* np = static_cast<const BvhNode4*>(nodes_v) + node;
