@@ -1,0 +1,60 @@
+"""GPU tier: every A/B build variant of the traversal kernels gives the same bits.
+
+The switches (B2PT_STEP, B2PT_TRIQ, B2PT_BVH4, B2PT_DEFER, B2PT_TRAVERSAL, B2PT_SMALL_CHUNKS, B2PT_COLLAPSE) are
+read once per process, so each variant runs in its own subprocess (tests/variant_probe.py): closest hits must
+equal the fp64 brute-force oracle bit for bit, and the occlusion answers, a frame in the reference's random
+sequence and an accumulated Philox image must be identical across variants — and across wave capacities."""
+import json
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+
+VARIANTS = {
+    "default": {},
+    "step0_first_node_step": {"B2PT_STEP": "0"},
+    "step1_fma_slabs": {"B2PT_STEP": "1"},
+    "step2_quantised_nodes": {"B2PT_STEP": "2"},
+    "step3_cooperative_fetch": {"B2PT_STEP": "3"},
+    "step4_four_256bit_loads": {"B2PT_STEP": "4"},
+    "triangle_queue": {"B2PT_TRIQ": "1"},
+    "binary_nodes_deferred": {"B2PT_BVH4": "0"},
+    "binary_nodes_fp64_in_kernel": {"B2PT_BVH4": "0", "B2PT_DEFER": "0"},
+    "thread_per_ray": {"B2PT_TRAVERSAL": "0"},
+    "fixed_collapse_big_chunks": {"B2PT_COLLAPSE": "fixed", "B2PT_SMALL_CHUNKS": "0"},
+    "occupancy_8": {"B2PT_OCC": "8"},
+}
+
+
+def _probe(env_extra):
+    env = dict(os.environ)
+    for k in list(env):
+        if k.startswith("B2PT_"):
+            del env[k]
+    env.update(env_extra)
+    p = subprocess.run([sys.executable, str(ROOT / "tests" / "variant_probe.py")], env=env, capture_output=True, text=True,
+                       timeout=600, cwd=str(ROOT))
+    assert p.returncode == 0, p.stderr[-2000:]
+    line = [l for l in p.stdout.splitlines() if l.startswith("VARIANT ")][-1]
+    return json.loads(line[len("VARIANT "):])
+
+
+@pytest.fixture(scope="module")
+def default_probe():
+    return _probe({})
+
+
+@pytest.mark.parametrize("name", list(VARIANTS))
+def test_variant_gives_the_same_bits(name, default_probe):
+    got = default_probe if name == "default" else _probe(VARIANTS[name])
+    assert got["closest_equals_oracle"], "closest hits differ from the fp64 brute force"
+    for key in ("any", "frame", "accum_auto"):
+        assert got[key] == default_probe[key], f"{key} differs from the default build"
+    assert got["accum_small_waves"] == got["accum_auto"], "the image depends on the wave capacity"
+    if name == "step2_quantised_nodes":
+        assert got["node_bytes"] == 64
