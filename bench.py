@@ -75,6 +75,17 @@ class ClockSampler:
                                          stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
+            return
+        # wait for the first sample: nvidia-smi's start-up (NVML attach, enumerating the box's GPUs) takes up to a
+        # second and stalls launches while it lasts — it must be over before anything is timed
+        t0 = time.time()
+        while time.time() - t0 < 5.0 and self.proc.poll() is None:
+            try:
+                if os.path.getsize(self.path) > 0:
+                    break
+            except OSError:
+                pass
+            time.sleep(0.05)
 
     def mark_begin(self):
         self.t_begin = time.time()
@@ -274,8 +285,11 @@ def run_b2pt(args, cfg):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     e0.record()
+    step_ms = []
     for k in range(args.steps):
-        step(k, 0)
+        ts = time.perf_counter()
+        step(k, 0)             # ends with a stream synchronize
+        step_ms.append((time.perf_counter() - ts) * 1e3)
     e1.record()
     barrier()
     wall_s = time.perf_counter() - t0
@@ -384,7 +398,7 @@ def run_b2pt(args, cfg):
             "mrays_per_s": float(rays[0].item() + rays[1].item()) / (dev_ms * 1e-3) / 1e6,
             "rays_per_sample": bpr["rays_per_sample"],   # rays really traced (K5 + K8)
             "shadow_rays_culled_frac": bpr["shadow_rays_culled_frac"],
-            "device_ms_render_max": render_ms, "wall_ms": wall_ms,
+            "step_ms_host": [round(x, 3) for x in step_ms], "device_ms_render_max": render_ms, "wall_ms": wall_ms,
             "image_mean": float(mean_img.mean()), "image_finite": bool(np.isfinite(mean_img).all()),
             "nan_samples": st["nan_pixels"],
             "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu}

@@ -95,8 +95,8 @@ __device__ __forceinline__ uint32_t warp_append(bool want, uint32_t* counter) {
 }
 
 // ---- K6 ----------------------------------------------------------------------
-template <class Rng>
-__global__ void __launch_bounds__(kThreads)
+template <class Rng, int MINB = 8>
+__global__ void __launch_bounds__(kThreads, MINB)
 k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restrict__ hits, SurfaceState sf,
           ShadowRays sh, uint32_t* __restrict__ queues, WaveCounts wc, uint32_t bounce, float* __restrict__ wave_out,
           TraceCounters* __restrict__ counters) {
@@ -378,8 +378,17 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
         const PathState& nxt = r->st[(b + 1) & 1];
         launch_closest(lc, sc, cur, wc.active + b, 0.0f, 100.0f, r->d_hits.get(), r->d_counters.get(), /*finish=*/false);   // tmin 0, tmax 100 (:652)
         mark(kClsClosest);
-        k_surface<Rng><<<grid, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
-                                                 wc, (uint32_t)b, r->d_wave_out.get(), r->d_counters.get());
+        // K6 waits on gathers (triangle, normals, material): A/B of resident blocks per SM, B2PT_SURF_OCC = 8 | 10 | 12
+        static const int socc = [] { const char* e = getenv("B2PT_SURF_OCC"); return e ? atoi(e) : 8; }();
+        if (socc >= 12)
+            k_surface<Rng, 12><<<r->sm_count * 12, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
+                                                                   wc, (uint32_t)b, r->d_wave_out.get(), r->d_counters.get());
+        else if (socc >= 10)
+            k_surface<Rng, 10><<<r->sm_count * 10, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
+                                                                   wc, (uint32_t)b, r->d_wave_out.get(), r->d_counters.get());
+        else
+            k_surface<Rng><<<grid, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
+                                                     wc, (uint32_t)b, r->d_wave_out.get(), r->d_counters.get());
         count();
         mark(kClsSurface);
         if (wp.n_lights > 0) {
@@ -388,9 +397,20 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
         }
         uint32_t* q = r->d_queues.get();
         const size_t cap = wp.capacity;
-        if (kinds[0]) { k_shade<kBsdfConductor, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 0 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
-        if (kinds[1]) { k_shade<kBsdfDiffuse, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 1 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
-        if (kinds[2]) { k_shade<kBsdfDielectric, Rng><<<grid, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 2 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+        // resident blocks per SM of the three lighter shade kernels: 8 (64 registers, a few spilled words) beats 6
+        // (80 registers) — they are bound by instruction issue with 24 warps per SM; c2 513 -> 536, c3 426 -> 449
+        // Msamples/s (A/B: B2PT_SHADE_OCC3 = 6 | 8)
+        static const int occ3 = [] { const char* e = getenv("B2PT_SHADE_OCC3"); return e ? atoi(e) : 8; }();
+        const int g3 = r->sm_count * (occ3 >= 8 ? 16 : 8);
+        if (occ3 >= 8) {
+            if (kinds[0]) { k_shade<kBsdfConductor, Rng, 8><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 0 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+            if (kinds[1]) { k_shade<kBsdfDiffuse, Rng, 8><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 1 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+            if (kinds[2]) { k_shade<kBsdfDielectric, Rng, 8><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 2 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+        } else {
+            if (kinds[0]) { k_shade<kBsdfConductor, Rng><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 0 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+            if (kinds[1]) { k_shade<kBsdfDiffuse, Rng><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 1 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+            if (kinds[2]) { k_shade<kBsdfDielectric, Rng><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 2 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+        }
         if (kinds[3]) {
             // the layered kernel waits on instruction fetch (4 500 instructions, twice the instruction cache):
             // more resident warps hide it better than more registers per thread help (A/B: B2PT_SHADE_OCC)
@@ -431,11 +451,13 @@ void render_frames(B2ptRenderer* r, int spp, bool accumulate) {
         log2cap = 20;
         while ((1ull << log2cap) < want && log2cap < 26) log2cap++;
         const size_t per_path = (size_t)(2 * kPathStateWords + kSurfaceStateWords + kShadowWords) * 4 + sizeof(HitRecord) + 16 + 12;
-        size_t free_b = 0, total_b = 0;
-        B2PT_CUDA(cudaMemGetInfo(&free_b, &total_b));
         const size_t held = r->d_hits.size();                      // paths the buffers hold now
-        const size_t have = held * per_path;                       // released before a larger allocation
-        while (log2cap > 20 && (per_path << log2cap) > (free_b + have) / 2) log2cap--;
+        if (((size_t)1 << log2cap) > held) {                       // growing: never more than half of the free memory
+            size_t free_b = 0, total_b = 0;                        // (asked only now: cudaMemGetInfo can take tens of ms
+            B2PT_CUDA(cudaMemGetInfo(&free_b, &total_b));          //  when a monitoring tool holds the driver)
+            const size_t have = held * per_path;                   // released before a larger allocation
+            while (log2cap > 20 && (per_path << log2cap) > (free_b + have) / 2) log2cap--;
+        }
         while (log2cap < 27 && ((size_t)1 << log2cap) < held) log2cap++;
     }
     B2PT_REQUIRE(log2cap >= 10 && log2cap <= 27, B2PT_E_INVALID, "wave_paths_log2 must be in [10, 27]");
