@@ -83,6 +83,7 @@ struct WarpPolicy {
     int q_break;        // trace_wideq: ... or when the warp's triangle queue holds this many entries
     int q_out;          // trace_wideq: leaves a lane may queue and keep descending (1 or 2)
     int small_chunks;   // 1: launches with fewer than 64 rays per warp use smaller chunks (ray_chunk_shift)
+    int any_unsorted;   // 1: occlusion rays visit the hit children of a wide node in slot order, not nearest first
 };
 
 // ... unless the launch is small.  The late bounces of a wave hold a few thousand rays (c2: 0.06 % of the paths

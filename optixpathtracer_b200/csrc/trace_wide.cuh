@@ -250,11 +250,13 @@ __device__ __forceinline__ void trace_wide(const void* __restrict__ nodes_v, con
                 int ck[4] = {ch.x, ch.y, ch.z, ch.w};
                 // sort the four (t, child) pairs by t, misses (t = inf) last: 5-comparator network
 #define B2PT_CSWAP(a, b) { if (tk[b] < tk[a]) { const float tt = tk[a]; tk[a] = tk[b]; tk[b] = tt; const int cc = ck[a]; ck[a] = ck[b]; ck[b] = cc; } }
-                B2PT_CSWAP(0, 1) B2PT_CSWAP(2, 3) B2PT_CSWAP(0, 2) B2PT_CSWAP(1, 3) B2PT_CSWAP(1, 2)
+                if (!(ANY && pol.any_unsorted)) {   // occlusion rays may skip the ordering (A/B: B2PT_ANY_UNSORTED)
+                    B2PT_CSWAP(0, 1) B2PT_CSWAP(2, 3) B2PT_CSWAP(0, 2) B2PT_CSWAP(1, 3) B2PT_CSWAP(1, 2)
+                }
 #undef B2PT_CSWAP
                 if (DIET && sp + 3 <= kSharedStack) {
-                    // sorted: a hit in slot k implies hits in the slots before it, so the three stores land
-                    // contiguously, farthest first; a store for a miss is overwritten by the next one
+                    // each store lands at the current top and the top only moves for a hit, so the entries are
+                    // contiguous, farthest first; a store for a miss is overwritten by the next one
                     s_stack[sp][tid] = ck[3]; sp += tk[3] < INFINITY ? 1 : 0;
                     s_stack[sp][tid] = ck[2]; sp += tk[2] < INFINITY ? 1 : 0;
                     s_stack[sp][tid] = ck[1]; sp += tk[1] < INFINITY ? 1 : 0;
