@@ -40,6 +40,7 @@ struct B2ptRenderer {
     b2pt::DeviceBuffer<float> d_words;         // backing store of all SoA float/u32 arrays
     b2pt::DeviceBuffer<b2pt::HitRecord> d_hits;
     b2pt::DeviceBuffer<uint32_t> d_queues;     // 4 material queues
+    b2pt::DeviceBuffer<uint32_t> d_queues2;    // ... ordered by light visibility (K7p)
     b2pt::DeviceBuffer<uint32_t> d_counts;     // per-bounce counters
     b2pt::DeviceBuffer<float> d_wave_out;      // per-path radiance of the current wave (3 planes)
     b2pt::DeviceBuffer<b2pt::TraceCounters> d_counters;

@@ -183,6 +183,47 @@ k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restri
     if ((threadIdx.x & 31) == 0 && n_culled) atomicAdd(&counters->shadow_culled, (unsigned long long)n_culled);
 }
 
+// ---- K7p: order each shade queue by light visibility ----------------------------------------
+// A hit whose shadow ray reached the light evaluates f(wo, wl) before it samples the BSDF; one whose ray was
+// blocked (or never sent) only samples.  For the layered BSDF that is six random walks against one, and a warp
+// with both kinds runs at the pace of the first: (5 v + 1) / 6 of its lanes busy for a visible fraction v.  This
+// pass rewrites each queue with the visible hits at the front and the others at the back (warp-aggregated
+// atomics on two cursors per queue), so all warps but one per queue are uniform.  Positions inside a queue never
+// enter a result (every output is addressed by the path's id), so the image bits do not change.  Only the
+// layered queue is reordered: c4 74 -> 89, c5 393 -> 493 Msamples/s.  For the three light BSDFs f costs about as
+// much as a sample, and reading the path state in scrambled order costs more than the idle lanes did
+// (c2 -5 %, c1 -9 % with all four queues reordered; B2PT_PARTITION=2 does that, 0 none).
+__global__ void __launch_bounds__(256)
+k_partition_queues(const uint32_t* __restrict__ queues, uint32_t* __restrict__ queues2, const uint32_t* __restrict__ info,
+                   WaveCounts wc, uint32_t bounce, uint32_t capacity, uint32_t* __restrict__ cursors /* [4][2], zeroed */,
+                   uint32_t first_kind) {
+    const uint32_t kind = blockIdx.y + first_kind;
+    const uint32_t n = wc.queued[4 * bounce + kind];
+    const uint32_t* q = queues + (size_t)kind * capacity;
+    uint32_t* q2 = queues2 + (size_t)kind * capacity;
+    uint32_t* cur = cursors + 2 * kind;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t iters = (n + stride - 1) / stride;
+    for (uint32_t it = 0; it < iters; it++) {
+        const uint32_t k = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        const bool valid = k < n;
+        const uint32_t i = valid ? q[k] : 0u;
+        const bool vis = valid && (info[i] & kInfoVisible) != 0;
+        const uint32_t mv = __ballot_sync(0xffffffffu, vis), mn = __ballot_sync(0xffffffffu, valid && !vis);
+        uint32_t bv = 0, bn = 0;
+        if (lane == 0) {
+            if (mv) bv = atomicAdd(cur, (uint32_t)__popc(mv));
+            if (mn) bn = atomicAdd(cur + 1, (uint32_t)__popc(mn));
+        }
+        bv = __shfl_sync(0xffffffffu, bv, 0);
+        bn = __shfl_sync(0xffffffffu, bn, 0);
+        const uint32_t below = (1u << lane) - 1u;
+        if (vis) q2[bv + (uint32_t)__popc(mv & below)] = i;
+        else if (valid) q2[n - 1u - (bn + (uint32_t)__popc(mn & below))] = i;
+    }
+}
+
 // ---- K7a-d -------------------------------------------------------------------
 // One launch per BSDF: every thread of the kernel runs the same BSDF code.
 template <int KIND, class Rng, int MINB = 6>
@@ -311,8 +352,9 @@ void layout_wave(B2ptRenderer* r, uint32_t capacity) {
     r->d_words.alloc(words);
     r->d_hits.alloc(capacity);
     r->d_queues.alloc((size_t)4 * capacity);
+    r->d_queues2.alloc((size_t)4 * capacity);
     r->d_wave_out.alloc((size_t)3 * capacity);
-    r->d_counts.alloc((size_t)5 * 100 + 1);   // active[<=100] + queued[<=99][4]
+    r->d_counts.alloc((size_t)5 * 100 + 1 + 8 * 100);   // active[<=100] + queued[<=99][4] + partition cursors[<=100][4][2]
     float* w = r->d_words.get();
     auto take = [&]() { float* p = w; w += capacity; return p; };
     for (int k = 0; k < 2; k++) {
@@ -397,6 +439,23 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
         }
         uint32_t* q = r->d_queues.get();
         const size_t cap = wp.capacity;
+        static const int partition = [] { const char* e = getenv("B2PT_PARTITION"); return e ? atoi(e) : 1; }();
+        uint32_t* q3 = q;   // the layered queue K7d reads
+        if (wp.n_lights > 0 && partition == 2) {          // K7p over all four queues (A/B only)
+            k_partition_queues<<<dim3((unsigned)(r->sm_count * 4), 4), 256, 0, s>>>(
+                r->d_queues.get(), r->d_queues2.get(), r->surf.info, wc, (uint32_t)b, wp.capacity,
+                r->d_counts.get() + 501 + 8 * b, 0u);
+            count();
+            mark(kClsShade);
+            q = q3 = r->d_queues2.get();
+        } else if (wp.n_lights > 0 && partition == 1 && kinds[3]) {   // K7p: visible hits first in the layered queue
+            k_partition_queues<<<dim3((unsigned)(r->sm_count * 4), 1), 256, 0, s>>>(
+                r->d_queues.get(), r->d_queues2.get(), r->surf.info, wc, (uint32_t)b, wp.capacity,
+                r->d_counts.get() + 501 + 8 * b, 3u);
+            count();
+            mark(kClsShade);
+            q3 = r->d_queues2.get();
+        }
         // resident blocks per SM of the three lighter shade kernels: 8 (64 registers, a few spilled words) beats 6
         // (80 registers) — they are bound by instruction issue with 24 warps per SM; c2 513 -> 536, c3 426 -> 449
         // Msamples/s (A/B: B2PT_SHADE_OCC3 = 6 | 8)
@@ -417,11 +476,11 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
             static const int occ = [] { const char* e = getenv("B2PT_SHADE_OCC"); return e ? atoi(e) : 8; }();
             const int g = r->sm_count * std::max(occ, 4) * 2;
             if (occ >= 8)
-                k_shade<kBsdfLayered, Rng, 8><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
+                k_shade<kBsdfLayered, Rng, 8><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
             else if (occ >= 6)
-                k_shade<kBsdfLayered, Rng, 6><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
+                k_shade<kBsdfLayered, Rng, 6><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
             else
-                k_shade<kBsdfLayered, Rng, 4><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
+                k_shade<kBsdfLayered, Rng, 4><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
             count();
             mark(kClsShade);
         }
@@ -450,7 +509,7 @@ void render_frames(B2ptRenderer* r, int spp, bool accumulate) {
         const uint64_t want = n_pixels * (uint64_t)std::max(spp, 1);
         log2cap = 20;
         while ((1ull << log2cap) < want && log2cap < 26) log2cap++;
-        const size_t per_path = (size_t)(2 * kPathStateWords + kSurfaceStateWords + kShadowWords) * 4 + sizeof(HitRecord) + 16 + 12;
+        const size_t per_path = (size_t)(2 * kPathStateWords + kSurfaceStateWords + kShadowWords) * 4 + sizeof(HitRecord) + 32 + 12;
         const size_t held = r->d_hits.size();                      // paths the buffers hold now
         if (((size_t)1 << log2cap) > held) {                       // growing: never more than half of the free memory
             size_t free_b = 0, total_b = 0;                        // (asked only now: cudaMemGetInfo can take tens of ms
