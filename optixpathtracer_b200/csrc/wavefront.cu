@@ -475,7 +475,11 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
             // more resident warps hide it better than more registers per thread help (A/B: B2PT_SHADE_OCC)
             static const int occ = [] { const char* e = getenv("B2PT_SHADE_OCC"); return e ? atoi(e) : 8; }();
             const int g = r->sm_count * std::max(occ, 4) * 2;
-            if (occ >= 8)
+            if (occ >= 12)
+                k_shade<kBsdfLayered, Rng, 12><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
+            else if (occ >= 10)
+                k_shade<kBsdfLayered, Rng, 10><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
+            else if (occ >= 8)
                 k_shade<kBsdfLayered, Rng, 8><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
             else if (occ >= 6)
                 k_shade<kBsdfLayered, Rng, 6><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
