@@ -214,7 +214,7 @@ k_any_p(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, fl
 // B2PT_TRAVERSAL=0 selects the first (thread-per-ray) kernels, for A/B measurements
 bool use_wide();
 int occ_blocks() {   // resident blocks per SM the traversal kernels are built and launched for
-    static const int v = [] { const char* e = getenv("B2PT_OCC"); return e ? atoi(e) : (use_wide() ? 6 : 8); }();
+    static const int v = [] { const char* e = getenv("B2PT_OCC"); return e ? atoi(e) : (use_wide() ? 7 : 8); }();
     return v;
 }
 WarpPolicy warp_policy() {
@@ -286,6 +286,8 @@ void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState&
             k_closest_w<false, 6, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (node_step() == 5 && occ_blocks() == 8)
             k_closest_w<false, 8, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 5 && occ_blocks() == 7)
+            k_closest_w<false, 7, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (lc.stats && node_step() == 4)
             k_closest_w<true, 4, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (node_step() == 4 && occ_blocks() == 6)
@@ -390,6 +392,8 @@ void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh
             k_any_w<false, 6, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (node_step() == 5 && occ_blocks() == 8)
             k_any_w<false, 8, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 5 && occ_blocks() == 7)
+            k_any_w<false, 7, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (lc.stats && node_step() == 4)
             k_any_w<true, 4, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (node_step() == 4 && occ_blocks() == 6)
