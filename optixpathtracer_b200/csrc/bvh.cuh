@@ -68,6 +68,17 @@ struct alignas(16) BvhNode4Q {
 };
 static_assert(sizeof(BvhNode4Q) == 64, "quantised wide node must be 64 bytes");
 
+// The 4-wide node in 96 bytes, three 256-bit loads per visit (B2PT_STEP=6): the same fp32 boxes, with the four
+// child indices hidden in the low mantissa byte of the sixteen x / y planes (child k = the low bytes of
+// lox[k], hix[k], loy[k], hiy[k], least significant first).  K3d rounds each of those planes OUTWARD to a value
+// whose low byte is the payload — at most 511 ulp, 2^-14 relative — so the traversal uses the planes as they
+// are, payload included, and still only prunes.  Empty slots: planes of +3e38 (finite: the payload must not
+// turn them into NaNs), child = kEmptyChild.
+struct alignas(32) BvhNode4P {
+    float4 lox, hix, loy, hiy, loz, hiz;   // component k = slot k
+};
+static_assert(sizeof(BvhNode4P) == 96, "packed wide node must be 96 bytes");
+
 struct alignas(16) TriRecord {
     float4 a;   // v0.x v0.y v0.z v1.x
     float4 b;   // v1.y v1.z v2.x v2.y

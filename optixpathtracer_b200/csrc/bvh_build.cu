@@ -349,6 +349,41 @@ __device__ __forceinline__ void quantise_axis(const float lo[4], const float hi[
         qhi |= (uint32_t)b << (8 * k);
     }
 }
+// BvhNode4P: the float nearest to v on the outward side (down: <= v, else >= v) whose low mantissa byte is `payload`.
+__device__ __forceinline__ float embed_byte(float v, uint32_t payload, bool down) {
+    const uint32_t u = __float_as_uint(v);
+    const uint32_t sign = u & 0x80000000u, m = u & 0x7fffffffu;
+    const bool grow = (sign != 0u) == down;   // the outward side is the larger magnitude
+    uint32_t w = (m & ~0xffu) | payload;
+    if (grow) {
+        if (w < m) w += 0x100u;
+        return __uint_as_float(sign | w);
+    }
+    if (w > m) {
+        if (m < 0x100u) return __uint_as_float((sign ^ 0x80000000u) | payload);   // cross zero: a denormal of the other sign
+        w -= 0x100u;
+    }
+    return __uint_as_float(sign | w);
+}
+__device__ __forceinline__ BvhNode4P pack4(const Slot4 sl[4]) {
+    float lx[4], hx[4], ly[4], hy[4], lz[4], hz[4];
+    for (int k = 0; k < 4; k++) {
+        const bool used = sl[k].child != kEmptyChild;
+        const uint32_t c = (uint32_t)sl[k].child;
+        const float big = 3.0e38f;
+        lx[k] = embed_byte(used ? sl[k].lx : big, c & 0xffu, true);
+        hx[k] = embed_byte(used ? sl[k].hx : big, (c >> 8) & 0xffu, false);
+        ly[k] = embed_byte(used ? sl[k].ly : big, (c >> 16) & 0xffu, true);
+        hy[k] = embed_byte(used ? sl[k].hy : big, (c >> 24) & 0xffu, false);
+        lz[k] = used ? sl[k].lz : big;
+        hz[k] = used ? sl[k].hz : big;
+    }
+    BvhNode4P p;
+    p.lox = make_float4(lx[0], lx[1], lx[2], lx[3]); p.hix = make_float4(hx[0], hx[1], hx[2], hx[3]);
+    p.loy = make_float4(ly[0], ly[1], ly[2], ly[3]); p.hiy = make_float4(hy[0], hy[1], hy[2], hy[3]);
+    p.loz = make_float4(lz[0], lz[1], lz[2], lz[3]); p.hiz = make_float4(hz[0], hz[1], hz[2], hz[3]);
+    return p;
+}
 __device__ __forceinline__ BvhNode4Q quantise4(const Slot4 sl[4]) {
     bool used[4];
     float lo[4], hi[4];
@@ -368,7 +403,7 @@ __device__ __forceinline__ BvhNode4Q quantise4(const Slot4 sl[4]) {
 
 __global__ void __launch_bounds__(kThreads)
 k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restrict__ wide, BvhNode4Q* __restrict__ wideq,
-            int greedy) {
+            BvhNode4P* __restrict__ widep, int greedy) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_nodes) return;
     const BvhNode2 nd = nodes[i];
@@ -409,6 +444,7 @@ k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restric
         sl[k].child = kEmptyChild;
     }
     if (wideq) wideq[i] = quantise4(sl);
+    if (widep) widep[i] = pack4(sl);
     BvhNode4 w;
     w.lox = make_float4(sl[0].lx, sl[1].lx, sl[2].lx, sl[3].lx); w.hix = make_float4(sl[0].hx, sl[1].hx, sl[2].hx, sl[3].hx);
     w.loy = make_float4(sl[0].ly, sl[1].ly, sl[2].ly, sl[3].ly); w.hiy = make_float4(sl[0].hy, sl[1].hy, sl[2].hy, sl[3].hy);
@@ -475,6 +511,7 @@ DeviceScene SceneBuffers::view() const {
     s.nodes = nodes.get();
     s.nodes4 = nodes4.get();
     s.nodes4q = nodes4q.get();
+    s.nodes4p = nodes4p.get();
     s.tris = tris.get();
     s.nrms = nrms.get();
     s.uvs = uvs.get();
@@ -491,7 +528,7 @@ DeviceScene SceneBuffers::view() const {
 }
 
 int64_t SceneBuffers::device_bytes() const {
-    return (int64_t)(nodes.bytes() + nodes4.bytes() + nodes4q.bytes() + tris.bytes() + nrms.bytes() + uvs.bytes() + materials.bytes() +
+    return (int64_t)(nodes.bytes() + nodes4.bytes() + nodes4q.bytes() + nodes4p.bytes() + tris.bytes() + nrms.bytes() + uvs.bytes() + materials.bytes() +
                      textures.bytes() + tri_order.bytes());
 }
 
@@ -607,6 +644,7 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
     out.nodes.alloc((size_t)out.n_nodes);
     out.nodes4.alloc((size_t)out.n_nodes);
     out.nodes4q.alloc((size_t)out.n_nodes);
+    out.nodes4p.alloc((size_t)out.n_nodes);
     out.tris.alloc((size_t)n);
     out.nrms.alloc((size_t)n);
     out.uvs.alloc(any_uv ? (size_t)n : 0);
@@ -695,7 +733,7 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
         k_emit_single<<<1, 1, 0, stream>>>(d_wv.get(), pad, out.nodes.get());
     }
     if (out.n_nodes > 0)
-        k_collapse4<<<blocks_for(out.n_nodes), kThreads, 0, stream>>>(out.n_nodes, out.nodes.get(), out.nodes4.get(), out.nodes4q.get(), collapse_greedy());
+        k_collapse4<<<blocks_for(out.n_nodes), kThreads, 0, stream>>>(out.n_nodes, out.nodes.get(), out.nodes4.get(), out.nodes4q.get(), out.nodes4p.get(), collapse_greedy());
     k_emit_tris<<<blocks_for(n), kThreads, 0, stream>>>(n, d_wv.get(), d_nrm.get(), order, d_tri_mesh.get(),
                                                          d_infos.get(), d_idx.get(), d_uv.get(),
                                                          out.tris.get(), out.nrms.get(), out.uvs.get());

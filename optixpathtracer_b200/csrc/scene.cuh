@@ -44,7 +44,8 @@ struct MeshInfo {
 struct DeviceScene {
     const BvhNode2* nodes;
     const BvhNode4* nodes4;         // the same tree, two levels per node (bvh.cuh)
-    const BvhNode4Q* nodes4q;       // ... and those in 64 bytes, child boxes quantised (what K5/K8 read)
+    const BvhNode4Q* nodes4q;       // ... and those in 64 bytes, child boxes quantised (B2PT_STEP=2)
+    const BvhNode4P* nodes4p;       // ... and in 96 bytes, child indices hidden in the planes' low bytes (B2PT_STEP=6)
     const TriRecord* tris;
     const NrmRecord* nrms;
     const UvRecord* uvs;            // nullptr when no mesh has texcoords
@@ -62,6 +63,7 @@ struct SceneBuffers {
     DeviceBuffer<BvhNode2> nodes;
     DeviceBuffer<BvhNode4> nodes4;
     DeviceBuffer<BvhNode4Q> nodes4q;
+    DeviceBuffer<BvhNode4P> nodes4p;
     DeviceBuffer<TriRecord> tris;
     DeviceBuffer<NrmRecord> nrms;
     DeviceBuffer<UvRecord> uvs;

@@ -135,7 +135,7 @@ k_closest_w(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active,
     if constexpr (Q)
         trace_wideq<false, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
     else
-        trace_wide<false, STATS, STEP>(STEP == 2 ? (const void*)sc.nodes4q : (const void*)sc.nodes4, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io, ts, pol);
+        trace_wide<false, STATS, STEP>(STEP == 2 ? (const void*)sc.nodes4q : STEP == 6 ? (const void*)sc.nodes4p : (const void*)sc.nodes4, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io, ts, pol);
     if (STATS) {
         atomicAdd(&counters->nodes, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris, (unsigned long long)ts.tris);
@@ -153,7 +153,7 @@ k_any_w(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, fl
     if constexpr (Q)
         trace_wideq<true, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
     else
-        trace_wide<true, STATS, STEP>(STEP == 2 ? (const void*)sc.nodes4q : (const void*)sc.nodes4, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io, ts, pol);
+        trace_wide<true, STATS, STEP>(STEP == 2 ? (const void*)sc.nodes4q : STEP == 6 ? (const void*)sc.nodes4p : (const void*)sc.nodes4, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io, ts, pol);
     if (STATS) {
         atomicAdd(&counters->nodes_any, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris_any, (unsigned long long)ts.tris);
@@ -236,11 +236,12 @@ bool use_wide() {   // 4-wide nodes for K5/K8 (scenes without an any-hit predica
     return v;
 }
 // B2PT_STEP selects the node step of trace_wide (all bit-exact, A/B in profiles/r01_ab_node_step.txt):
-// 5 = fp32 nodes, FMA-form slabs, three 256-bit loads + one 128-bit load of the child indices (default);
+// 6 = 96-byte nodes with the child indices in the planes' low mantissa bytes: three 256-bit loads
+// (default); 5 = 128-byte nodes, three 256-bit loads + one 128-bit load of the child indices;
 // 4 = four 256-bit loads (reads the 16 pad bytes too); 3 = warp-cooperative cp.async fetch (slower);
 // 2 = 64-byte quantised nodes (issue-bound, slower); 1 = FMA-form slabs, seven 128-bit loads; 0 = the first step
 int node_step() {
-    static const int v = [] { const char* e = getenv("B2PT_STEP"); return e ? atoi(e) : 5; }();
+    static const int v = [] { const char* e = getenv("B2PT_STEP"); return e ? atoi(e) : 6; }();
     return v;
 }
 bool use_triq() {   // B2PT_TRIQ=1: warp-shared triangle queue (trace_wideq.cuh) — bit-exact, measured 2-5 % slower, kept for A/B
@@ -262,7 +263,7 @@ int trace_grid_blocks_per_sm() { return occ_blocks() > 0 ? occ_blocks() : 8; }
 
 int trace_node_bytes(const DeviceScene& sc) {
     if (use_persistent() && use_wide() && sc.any_alpha_texture == 0)
-        return node_step() == 2 && !use_triq() ? (int)sizeof(BvhNode4Q) : (int)sizeof(BvhNode4);
+        return use_triq() ? (int)sizeof(BvhNode4) : node_step() == 2 ? (int)sizeof(BvhNode4Q) : node_step() == 6 ? (int)sizeof(BvhNode4P) : (int)sizeof(BvhNode4);
     return (int)sizeof(BvhNode2);
 }
 
@@ -280,6 +281,14 @@ void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState&
             k_closest_w<false, 6, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (tq)
             k_closest_w<false, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (lc.stats && node_step() == 6)
+            k_closest_w<true, 4, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 6 && occ_blocks() == 6)
+            k_closest_w<false, 6, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 6 && occ_blocks() == 7)
+            k_closest_w<false, 7, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+        else if (node_step() == 6 && occ_blocks() == 8)
+            k_closest_w<false, 8, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (lc.stats && node_step() == 5)
             k_closest_w<true, 4, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (node_step() == 5 && occ_blocks() == 6)
@@ -386,6 +395,14 @@ void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh
             k_any_w<false, 6, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (tq)
             k_any_w<false, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (lc.stats && node_step() == 6)
+            k_any_w<true, 4, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 6 && occ_blocks() == 6)
+            k_any_w<false, 6, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 6 && occ_blocks() == 7)
+            k_any_w<false, 7, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+        else if (node_step() == 6 && occ_blocks() == 8)
+            k_any_w<false, 8, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (lc.stats && node_step() == 5)
             k_any_w<true, 4, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (node_step() == 5 && occ_blocks() == 6)

@@ -58,6 +58,8 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 // indices — the pad bytes of the node are not read.  ncu: a divergent 256-bit load is not free, the L1TEX
 // data pipe still moves it as more than one wavefront (8.3 M wavefronts per SM against 9.0 M for the 128-bit
 // form on the same launch), but the launch is 6-8 % shorter.
+// STEP = 6: the 96-byte node BvhNode4P (child indices in the low mantissa bytes of the x / y planes): three
+// 256-bit loads per visit.
 // STEP = 3: DIET over the fp32 nodes, fetched by the warp TOGETHER.  A lane's seven 16-byte loads of its own
 // node cost seven L1TEX wavefronts — divergent lanes, one wavefront per lane per instruction, 16 of the
 // pipe's 128 bytes used; ncu of the fp32 step: L1TEX 88 % busy, long-scoreboard 5.1 of 10.6 cycles per
@@ -221,6 +223,18 @@ __device__ __forceinline__ void trace_wide(const void* __restrict__ nodes_v, con
                     const float4 chf = sn[6 ^ sw];
                     ch = make_int4(__float_as_int(chf.x), __float_as_int(chf.y), __float_as_int(chf.z), __float_as_int(chf.w));
                     B2PT_SLAB4F(0, x) B2PT_SLAB4F(1, y) B2PT_SLAB4F(2, z) B2PT_SLAB4F(3, w)
+                } else if constexpr (STEP == 6) {
+                    const BvhNode4P* np = static_cast<const BvhNode4P*>(nodes_v) + node;
+                    float4 lox, hix, loy, hiy, loz, hiz;
+                    ldg256(&np->lox, lox, hix);
+                    ldg256(&np->loy, loy, hiy);
+                    ldg256(&np->loz, loz, hiz);
+                    // child k = the low bytes of lox[k], hix[k], loy[k], hiy[k]
+#define B2PT_CHILD(c) ((int)__byte_perm(__byte_perm(__float_as_uint(lox.c), __float_as_uint(hix.c), 0x0040u),   \
+                                        __byte_perm(__float_as_uint(loy.c), __float_as_uint(hiy.c), 0x0040u), 0x5410u))
+                    ch = make_int4(B2PT_CHILD(x), B2PT_CHILD(y), B2PT_CHILD(z), B2PT_CHILD(w));
+#undef B2PT_CHILD
+                    B2PT_SLAB4F(0, x) B2PT_SLAB4F(1, y) B2PT_SLAB4F(2, z) B2PT_SLAB4F(3, w)
                 } else if constexpr (STEP == 4 || STEP == 5) {
                     const BvhNode4* np = static_cast<const BvhNode4*>(nodes_v) + node;
                     float4 lox, hix, loy, hiy, loz, hiz;
@@ -283,6 +297,8 @@ __device__ __forceinline__ void trace_wide(const void* __restrict__ nodes_v, con
                 const int slot = ~pend;
                 pend = 0;
                 if (STATS) ts.tris++;
+                // (reading the 48-byte record as one 256-bit + one 128-bit load, chosen by the slot's parity, was
+                // measured 1-2 % slower than these three loads: profiles/r01_ab_node_step.txt)
                 const TriRecord* tp = tris + slot;
                 const float4 ta = B2PT_LDG4(&tp->a);
                 const float4 tb = B2PT_LDG4(&tp->b);

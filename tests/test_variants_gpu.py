@@ -22,6 +22,8 @@ VARIANTS = {
     "step2_quantised_nodes": {"B2PT_STEP": "2"},
     "step3_cooperative_fetch": {"B2PT_STEP": "3"},
     "step4_four_256bit_loads": {"B2PT_STEP": "4"},
+    "step5_three_256bit_loads_plus_children": {"B2PT_STEP": "5"},
+    "step6_packed_96_byte_nodes": {"B2PT_STEP": "6"},
     "triangle_queue": {"B2PT_TRIQ": "1"},
     "binary_nodes_deferred": {"B2PT_BVH4": "0"},
     "binary_nodes_fp64_in_kernel": {"B2PT_BVH4": "0", "B2PT_DEFER": "0"},
@@ -58,3 +60,5 @@ def test_variant_gives_the_same_bits(name, default_probe):
     assert got["accum_small_waves"] == got["accum_auto"], "the image depends on the wave capacity"
     if name == "step2_quantised_nodes":
         assert got["node_bytes"] == 64
+    if name == "step6_packed_96_byte_nodes":
+        assert got["node_bytes"] == 96
