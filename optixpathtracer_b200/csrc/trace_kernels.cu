@@ -227,7 +227,7 @@ WarpPolicy warp_policy() {
         q_out = q_out < 1 ? 1 : (q_out > kQMaxOut - 1 ? kQMaxOut - 1 : q_out);
         const char* sc = getenv("B2PT_SMALL_CHUNKS");
         const char* au = getenv("B2PT_ANY_UNSORTED");
-        return WarpPolicy{a ? atoi(a) : 8, b ? atoi(b) : 20, q ? atoi(q) : 32, q_out, sc ? atoi(sc) : 1, au ? atoi(au) : 0};
+        return WarpPolicy{a ? atoi(a) : 8, b ? atoi(b) : 16, q ? atoi(q) : 32, q_out, sc ? atoi(sc) : 1, au ? atoi(au) : 1};
     }();
     return v;
 }

@@ -30,6 +30,7 @@ VARIANTS = {
     "thread_per_ray": {"B2PT_TRAVERSAL": "0"},
     "fixed_collapse_big_chunks": {"B2PT_COLLAPSE": "fixed", "B2PT_SMALL_CHUNKS": "0"},
     "occupancy_8": {"B2PT_OCC": "8"},
+    "any_hit_nearest_first_break_20": {"B2PT_ANY_UNSORTED": "0", "B2PT_BREAK": "20"},
 }
 
 
