@@ -136,6 +136,48 @@ def lights_array(lights):
     return arr
 
 
+def host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def use_all_host_cores() -> int:
+    """The CPU arm runs on every core this process may use.  torch.distributed.run exports OMP_NUM_THREADS=1
+    to its workers, which made round 1's N>1 reference lines single-threaded: the count is set explicitly,
+    in the environment (read by libgomp when liboracle_ref.so pulls it in) and through omp_set_num_threads
+    (for a libgomp some other module already loaded)."""
+    n = host_cores()
+    os.environ["OMP_NUM_THREADS"] = str(n)
+    os.environ.pop("OMP_THREAD_LIMIT", None)
+    try:
+        C.CDLL("libgomp.so.1", mode=C.RTLD_GLOBAL).omp_set_num_threads(C.c_int(n))
+    except OSError:
+        pass
+    return n
+
+
+def spp_per_gpu(args) -> int:
+    """weak: every GPU renders --spp-per-step samples of every pixel per step; strong: the step's samples are split."""
+    if args.scaling == "strong":
+        assert args.spp_per_step % args.gpus == 0, "--spp-per-step must be a multiple of --gpus for strong scaling"
+        return args.spp_per_step // args.gpus
+    return args.spp_per_step
+
+
+def workload_config(args, cfg, scene) -> dict:
+    """The `config` object of the JSON line: the workload only (no device facts), so that the b2pt arm and
+    the reference arm print the same dict for the same --config."""
+    label, spec, w, h, spp_total, depth, mode = cfg
+    return {"workload": label, "config_id": args.config, "width": w, "height": h,
+            "spp_per_step_per_gpu": spp_per_gpu(args), "spp_config": spp_total, "max_depth": depth, "bsdf_mode": mode,
+            "triangles": int(sum(len(np.asarray(m["indices"]).reshape(-1, 3)) for m in scene["meshes"])),
+            "lights": len(scene["lights"]), "scaling": args.scaling,
+            "l2": "inputs larger than L2: the path state of one step (>= 1 GB SoA) streams through HBM; the scene "
+                  "(16 MB BVH+triangles for c1-c4, 333 MB for c5) is re-read by every ray"}
+
+
 def cpu_reference_run(scene, w, h, depth, mode_id, target_s: float, steps: int, warmup: int):
     """Times the reference's own integrator + BSDF code compiled for the host
     (oracle/_ref, OpenMP over all host cores; optixTrace served by the oracle's
@@ -143,6 +185,7 @@ def cpu_reference_run(scene, w, h, depth, mode_id, target_s: float, steps: int, 
     frame.  Returns (Msamples/s, cores, sample description, Mrays/s, ms per step)."""
     from tests.util import RefOracle, fp
     from optixpathtracer_b200.api import _SceneMarshal
+    use_all_host_cores()
     ro = RefOracle()
     lib = ro.lib
     m = _SceneMarshal(scene)
@@ -193,8 +236,8 @@ def run_reference(args, cfg):
                                                           args.steps, args.warmup)
     line = {"impl": "reference", "metric": "Msamples/s", "value": msps, "unit": "Msamples/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": label, "bsdf_mode": mode, "max_depth": depth},
+            "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, cfg, scene),
             "cpu_baseline": {"value": msps, "unit": "Msamples/s", "cores": cores, "kind": "reference", "sample": desc,
                              "mrays_per_s": mrays},
             "e2e": {"value": msps, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -244,7 +287,8 @@ def run_b2pt(args, cfg):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     n_gpus = world
-    spp = args.spp_per_step
+    assert args.gpus == world, f"--gpus {args.gpus} but WORLD_SIZE is {world}"
+    spp = spp_per_gpu(args)
     scene = make_scene(spec)
     n_px = w * h
 
@@ -279,7 +323,7 @@ def run_b2pt(args, cfg):
         step(k, 1_000_000)
     total.zero_()
     r.ResetStats()
-    r.SetKernelTiming(True)
+    r.SetKernelTiming(False)       # `value` is timed without the per-kernel events; shares come from a separate pass below
     barrier()
     sampler.mark_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -296,7 +340,6 @@ def run_b2pt(args, cfg):
     clocks = sampler.stop() if rank == 0 else {}
     dev_ms = e0.elapsed_time(e1)
     st = r.Stats()
-    r.SetKernelTiming(False)
     t = torch.tensor([dev_ms, st["device_ms_render"], wall_s * 1e3], device=f"cuda:{local}", dtype=torch.float64)
     rays = torch.tensor([st["radiance_rays"], st["shadow_rays_traced"], st["kernel_launches"]], device=f"cuda:{local}", dtype=torch.float64)
     if world > 1:
@@ -335,6 +378,18 @@ def run_b2pt(args, cfg):
     h2d = 12 + 64 + 64 + 24 * len(scene["lights"])
     d2h = n_px * 12
 
+    # ---- attribution pass (untimed): the same steps with one CUDA event after every kernel ---------------
+    r.ResetStats()
+    r.SetKernelTiming(True)
+    n_attr = min(args.steps, 2)
+    for k in range(n_attr):
+        r.ClearAccumulation()
+        r.SetFrameId((k * n_gpus + rank) * spp)
+        r.RenderAccumulate(spp, download=False)
+    st_attr = r.Stats()
+    r.SetKernelTiming(False)
+    timing_overhead = st_attr["device_ms_render"] / n_attr / max(render_ms / args.steps, 1e-9) - 1.0
+
     if rank != 0:
         r.close()
         if world > 1:
@@ -348,9 +403,10 @@ def run_b2pt(args, cfg):
     else:
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     bpr = algorithmic_bytes_per_ray(scene, w, h, depth, mode, spp=1)
-    ms_k, n_k = st["device_ms_kernel"], st["launches_kernel"]
+    ms_k, n_k = st_attr["device_ms_kernel"], st_attr["launches_kernel"]
+    attr_ms = max(st_attr["device_ms_render"], 1e-9)
     closest_ms = max(ms_k[0], 1e-9)
-    achieved = st["radiance_rays"] * bpr["closest"] / (closest_ms * 1e-3) / 1e9
+    achieved = st_attr["radiance_rays"] * bpr["closest"] / (closest_ms * 1e-3) / 1e9
     traffic = None
     tpath = ROOT / "profiles" / "traffic.json"
     if tpath.exists():
@@ -358,18 +414,20 @@ def run_b2pt(args, cfg):
             tj = json.load(open(tpath)).get(args.config, {})
             traffic = tj.get("k_closest_dram_bytes_per_launch")
             if traffic is None and tj.get("k_closest_dram_bytes_per_ray") is not None:   # per ray (ncu) x rays of the average launch
-                traffic = tj["k_closest_dram_bytes_per_ray"] * st["radiance_rays"] / max(n_k[0], 1)
+                traffic = tj["k_closest_dram_bytes_per_ray"] * st_attr["radiance_rays"] / max(n_k[0], 1)
         except Exception:
             traffic = None
     roofline = {"kernel": "k_closest (K5 closest-hit BVH traversal)", "bound": "hbm", "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "bytes_per_ray": bpr["closest"], "nodes_per_ray": bpr["nodes_per_ray"], "tris_per_ray": bpr["tris_per_ray"],
                 "simd_node_loop": bpr["simd_node_loop"], "simd_tri_loop": bpr["simd_tri_loop"],
-                "bytes_per_launch": st["radiance_rays"] * bpr["closest"] / max(n_k[0], 1),
+                "bytes_per_launch": st_attr["radiance_rays"] * bpr["closest"] / max(n_k[0], 1),
                 "ms_per_launch": closest_ms / max(n_k[0], 1), "launches": n_k[0],
-                "share_of_step": {"closest": ms_k[0] / render_ms, "any": ms_k[1] / render_ms, "surface": ms_k[2] / render_ms,
-                                  "shade": ms_k[3] / render_ms, "other": ms_k[4] / render_ms},
-                "shadow": {"achieved": st["shadow_rays_traced"] * bpr["any"] / (max(ms_k[1], 1e-9) * 1e-3) / 1e9,
+                "share_of_step": {"closest": ms_k[0] / attr_ms, "any": ms_k[1] / attr_ms, "surface": ms_k[2] / attr_ms,
+                                  "shade": ms_k[3] / attr_ms, "other": ms_k[4] / attr_ms},
+                "attribution": f"separate pass of {n_attr} steps with a CUDA event after every kernel (off while `value` is timed); "
+                               f"that pass ran {timing_overhead * 100:+.2f} % against the timed steps",
+                "shadow": {"achieved": st_attr["shadow_rays_traced"] * bpr["any"] / (max(ms_k[1], 1e-9) * 1e-3) / 1e9,
                            "bytes_per_ray": bpr["any"]},
                 "note": "algorithmic bytes (nodes + triangles a ray must read) are served by L1/L2 — the README scenes' BVH is "
                         "16 MB, L2 holds 126 MB — so frac can exceed 1; DRAM sees only the ray/hit I/O (`traffic`, ~40 B/ray). "
@@ -385,14 +443,13 @@ def run_b2pt(args, cfg):
             cpu = {"value": None, "unit": "Msamples/s", "cores": 0, "kind": "reference", "sample": f"unavailable: {e}"}
 
     line = {"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": n_gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": label, "config_id": args.config, "width": w, "height": h, "spp_per_step_per_gpu": spp,
-                       "spp_config": spp_total, "max_depth": depth, "bsdf_mode": mode, "rng": "philox",
-                       "triangles": st["n_triangles"], "bvh_nodes": st["n_nodes"], "bvh_build_ms": build_ms,
-                       "scene_device_bytes": st["scene_device_bytes"], "wave_paths_log2": args.wave_log2 or "auto (one wave per step, <= 2^26 paths)",
-                       "parallelism": f"spp-split x{n_gpus}, replicated BVH, one NCCL reduce per step" if n_gpus > 1 else "single GPU",
-                       "l2": "path state of a wave (~1 GB SoA) exceeds L2; the 16 MB BVH is L2-resident by nature of the workload"},
+            "config": workload_config(args, cfg, scene),
+            "device": {"rng": "philox", "bvh_nodes": st["n_nodes"], "bvh_build_ms": build_ms,
+                       "scene_device_bytes": st["scene_device_bytes"],
+                       "wave_paths_log2": args.wave_log2 or "auto (one wave per step, <= 2^26 paths)",
+                       "parallelism": f"spp-split x{n_gpus}, replicated BVH, one NCCL reduce per step" if n_gpus > 1 else "single GPU"},
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(rays[2].item()),
             "mrays_per_s": float(rays[0].item() + rays[1].item()) / (dev_ms * 1e-3) / 1e6,
@@ -435,7 +492,9 @@ def main():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b2pt", choices=["b2pt", "reference"])
-    ap.add_argument("--config", default="c2", choices=sorted(CONFIGS))
+    ap.add_argument("--config", default="c4", choices=sorted(CONFIGS))
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every GPU renders --spp-per-step samples per step; strong: the step's samples are split over the GPUs")
     ap.add_argument("--spp-per-step", type=int, default=64)
     ap.add_argument("--wave-log2", type=int, default=0)
     ap.add_argument("--cpu-seconds", type=float, default=None, help="CPU work per reference step / baseline sample")

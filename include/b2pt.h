@@ -258,6 +258,10 @@ int b2pt_trace_any(B2ptRenderer* r, int64_t n, const float* org, const float* di
  * shading space, z = normal).  `seed` is the LCG state on entry (rng policy
  * = lcg_mode, B2PT_RNG_LCG_DEVICE or _HOST); seed_out (may be NULL) is the
  * state on return, so draw counts are checked too.
+ * lcg_mode = B2PT_RNG_PHILOX with bsdf = B2PT_BSDF_LAYERED runs the per-lane
+ * logic of the production walk engine instead (csrc/fast_layered.cuh): seed
+ * keys the Philox streams, seed_out is zeroed, and `sample` reports
+ * f = weight / |wi.z| with pdf = 1 (the engine only forms f |cos| / pdf).
  *   f      : n*3 out
  *   sample : ok[n] (0/1), f n*3, wi n*3, pdf n, flags n
  *            (bit0 reflection, bit1 transmission, bit2 specular, bit3 glossy)

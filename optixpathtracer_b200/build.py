@@ -38,7 +38,10 @@ NVCC_FLAGS = [
 # performs, which keeps peaked microfacet lobes (alpha ~ 0.01, condition number
 # ~1e5) within the 1e-5 parity bar.  Traversal keeps FMA (its deciding test uses
 # explicit fp64 intrinsics and is exact by construction).
-PER_FILE_FLAGS = {"wavefront.cu": ["-fmad=false"], "bsdf_hooks.cu": ["-fmad=false"]}
+# The walk engine of the production (Philox) generator is not bit-compatible with the reference by design
+# (fast_layered.cuh) and is built with FMA contraction and the approximate division / sqrt / exp / sin / cos.
+PER_FILE_FLAGS = {"wavefront.cu": ["-fmad=false"], "bsdf_hooks.cu": ["-fmad=false"],
+                  "shade_layered.cu": ["--use_fast_math"]}
 
 
 def _sources() -> list[Path]:

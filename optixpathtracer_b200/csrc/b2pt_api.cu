@@ -81,6 +81,15 @@ int b2pt_create(const B2ptSceneDesc* scene, const B2ptConfig* cfg, B2ptRenderer*
     if (cfg) r->cfg = *cfg; else b2pt_default_config(&r->cfg);
     r->device = r->cfg.device;
     int rc = guarded(nullptr, [&] {
+        // the same ranges the setters enforce: the per-bounce counters are laid out for at most 99 bounces and
+        // an unknown BSDF mode would match no shade queue (its paths would never write their result)
+        const B2ptConfig& c = r->cfg;
+        B2PT_REQUIRE(c.max_bounces >= 0 && c.max_bounces <= 99, B2PT_E_INVALID, "max_bounces must be in [0, 99]");
+        B2PT_REQUIRE(c.bsdf_mode >= B2PT_BSDF_AUTO && c.bsdf_mode <= B2PT_BSDF_LAYERED, B2PT_E_INVALID, "bad bsdf mode");
+        B2PT_REQUIRE(c.rng_mode >= B2PT_RNG_PHILOX && c.rng_mode <= B2PT_RNG_LCG_HOST, B2PT_E_INVALID, "bad rng mode");
+        B2PT_REQUIRE(c.wave_paths_log2 == 0 || (c.wave_paths_log2 >= 10 && c.wave_paths_log2 <= 27), B2PT_E_INVALID,
+                     "wave_paths_log2 must be 0 (auto) or in [10, 27]");
+        B2PT_REQUIRE(c.bvh_leaf_size >= 0 && c.bvh_leaf_size <= 8, B2PT_E_INVALID, "bvh_leaf_size must be in [0, 8]");
         int n_dev = 0;
         B2PT_CUDA(cudaGetDeviceCount(&n_dev));
         B2PT_REQUIRE(r->device >= 0 && r->device < n_dev, B2PT_E_INVALID, "device ordinal out of range");

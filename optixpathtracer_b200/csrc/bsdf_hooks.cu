@@ -5,6 +5,7 @@
 
 #include "bsdf_rows.cuh"
 #include "host_util.h"
+#include "wave_common.cuh"
 
 using namespace b2pt;
 
@@ -46,7 +47,11 @@ int hook_guard(int device, F&& f) {
 }
 
 bool bad_bsdf(int b) { return b < B2PT_BSDF_CONDUCTOR || b > B2PT_BSDF_LAYERED; }
-bool bad_lcg(int m) { return m != B2PT_RNG_LCG_DEVICE && m != B2PT_RNG_LCG_HOST; }
+// rng PHILOX selects the production walk engine's per-lane logic (fast_layered.cuh); only the layered BSDF has one
+bool bad_lcg(int m, int bsdf) {
+    if (m == B2PT_RNG_PHILOX) return bsdf != B2PT_BSDF_LAYERED;
+    return m != B2PT_RNG_LCG_DEVICE && m != B2PT_RNG_LCG_HOST;
+}
 int blocks(int64_t n) { return (int)((n + 127) / 128); }
 
 }  // namespace
@@ -56,7 +61,7 @@ extern "C" {
 int b2pt_bsdf_f(int32_t device, int32_t bsdf, int32_t lcg_mode, int64_t n, const float* albedo,
                 const float* roughness, const float* wo, const float* wi, const uint32_t* seed, float* f_out,
                 uint32_t* seed_out) {
-    if (n < 0 || bad_bsdf(bsdf) || bad_lcg(lcg_mode) || (n > 0 && (!albedo || !roughness || !wo || !wi || !f_out)))
+    if (n < 0 || bad_bsdf(bsdf) || bad_lcg(lcg_mode, bsdf) || (n > 0 && (!albedo || !roughness || !wo || !wi || !f_out)))
         return B2PT_E_INVALID;
     if (n == 0) return B2PT_OK;
     return hook_guard(device, [&] {
@@ -68,7 +73,10 @@ int b2pt_bsdf_f(int32_t device, int32_t bsdf, int32_t lcg_mode, int64_t n, const
         if (!seed) { zeros.assign((size_t)n, 0u); seed = zeros.data(); }
         d_s.upload(seed, (size_t)n);
         d_f.alloc((size_t)n * 3); d_so.alloc((size_t)n);
-        if (lcg_mode == B2PT_RNG_LCG_HOST)
+        d_so.zero();
+        if (lcg_mode == B2PT_RNG_PHILOX)
+            launch_fast_layered_rows_f(n, d_a.get(), d_r.get(), d_wo.get(), d_wi.get(), d_s.get(), d_f.get());
+        else if (lcg_mode == B2PT_RNG_LCG_HOST)
             k_bsdf_f<LcgRng<true>><<<blocks(n), 128>>>(bsdf, n, d_a.get(), d_r.get(), d_wo.get(), d_wi.get(), d_s.get(), d_f.get(), d_so.get());
         else
             k_bsdf_f<LcgRng<false>><<<blocks(n), 128>>>(bsdf, n, d_a.get(), d_r.get(), d_wo.get(), d_wi.get(), d_s.get(), d_f.get(), d_so.get());
@@ -81,7 +89,7 @@ int b2pt_bsdf_f(int32_t device, int32_t bsdf, int32_t lcg_mode, int64_t n, const
 int b2pt_bsdf_sample(int32_t device, int32_t bsdf, int32_t lcg_mode, int64_t n, const float* albedo,
                      const float* roughness, const float* wo, const uint32_t* seed, uint8_t* ok, float* f_out,
                      float* wi_out, float* pdf_out, uint8_t* flags_out, uint32_t* seed_out) {
-    if (n < 0 || bad_bsdf(bsdf) || bad_lcg(lcg_mode) ||
+    if (n < 0 || bad_bsdf(bsdf) || bad_lcg(lcg_mode, bsdf) ||
         (n > 0 && (!albedo || !roughness || !wo || !seed || !ok || !f_out || !wi_out || !pdf_out || !flags_out)))
         return B2PT_E_INVALID;
     if (n == 0) return B2PT_OK;
@@ -93,7 +101,11 @@ int b2pt_bsdf_sample(int32_t device, int32_t bsdf, int32_t lcg_mode, int64_t n, 
         d_s.upload(seed, (size_t)n);
         d_f.alloc((size_t)n * 3); d_wi.alloc((size_t)n * 3); d_p.alloc((size_t)n);
         d_so.alloc((size_t)n); d_ok.alloc((size_t)n); d_fl.alloc((size_t)n);
-        if (lcg_mode == B2PT_RNG_LCG_HOST)
+        d_so.zero();
+        if (lcg_mode == B2PT_RNG_PHILOX)
+            launch_fast_layered_rows_sample(n, d_a.get(), d_r.get(), d_wo.get(), d_s.get(), d_ok.get(), d_f.get(), d_wi.get(),
+                                            d_p.get(), d_fl.get());
+        else if (lcg_mode == B2PT_RNG_LCG_HOST)
             k_bsdf_sample<LcgRng<true>><<<blocks(n), 128>>>(bsdf, n, d_a.get(), d_r.get(), d_wo.get(), d_s.get(), d_ok.get(), d_f.get(), d_wi.get(), d_p.get(), d_fl.get(), d_so.get());
         else
             k_bsdf_sample<LcgRng<false>><<<blocks(n), 128>>>(bsdf, n, d_a.get(), d_r.get(), d_wo.get(), d_s.get(), d_ok.get(), d_f.get(), d_wi.get(), d_p.get(), d_fl.get(), d_so.get());

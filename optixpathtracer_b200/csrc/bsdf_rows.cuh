@@ -5,6 +5,7 @@
 
 #include "../../include/b2pt.h"
 #include "bsdf.cuh"
+#include "fast_layered.cuh"
 
 namespace b2pt {
 
@@ -59,6 +60,62 @@ B2PT_HD void bsdf_row_sample(int bsdf, int64_t i, const float* albedo, const flo
     pdf_out[i] = good ? s.pdf : 0.0f;
     flags_out[i] = good ? (uint8_t)s.flags : 0;
     if (seed_out) seed_out[i] = rng.s;
+}
+
+// ---- rows of the production (Philox) walk engine, fast_layered.cuh: one whole shade per row --------------------
+// seed[i] keys the streams the way a render does with (pixel, sample) = (seed, row).
+B2PT_HD fastlayer::WalkKey fast_row_key(uint32_t seed, int64_t i, uint32_t walk) {
+    fastlayer::WalkKey k;
+    k.k0 = seed;
+    k.k1 = (uint32_t)i * 0x9E3779B9u;
+    k.c1 = fastlayer::kStageWalk << 16;
+    k.c2 = walk;
+    return k;
+}
+// f = entrance reflection + (sum of the five walks) / 5; exactly 0 across the surface
+B2PT_HD float3 fast_layered_f(float3 albedo, float roughness, float3 wo, float3 wi, uint32_t seed, int64_t row) {
+    if (!(wo.z * wi.z > 0.0f)) return v3(0.0f);
+    float3 sum = v3(0.0f);
+    for (int w = 0; w < fastlayer::kWalks; w++) {
+        fastlayer::Walk k;
+        fastlayer::walk_begin_f(k, wo, wi, albedo, roughness);
+        const fastlayer::WalkKey key = fast_row_key(seed, row, (uint32_t)w);
+        while (fastlayer::walk_step(k, key)) {}
+        sum += k.f;
+    }
+    fastlayer::Walk k0;
+    fastlayer::walk_begin_f(k0, wo, wi, albedo, roughness);
+    return v3(fastlayer::entrance_reflection(k0.wo, k0.wi, k0.alpha)) + sum * (1.0f / (float)fastlayer::kWalks);
+}
+B2PT_HD void fast_layered_row_f(int64_t i, const float* albedo, const float* roughness, const float* wo, const float* wi,
+                                const uint32_t* seed, float* f_out) {
+    const float3 f = fast_layered_f(v3(albedo[3 * i], albedo[3 * i + 1], albedo[3 * i + 2]), roughness[i],
+                                    v3(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]), v3(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]),
+                                    seed ? seed[i] : 0u, i);
+    f_out[3 * i] = f.x;
+    f_out[3 * i + 1] = f.y;
+    f_out[3 * i + 2] = f.z;
+}
+// the sample walk: wi and the weight f |cos| / pdf, reported as f = weight / |wi.z|, pdf = 1
+B2PT_HD void fast_layered_row_sample(int64_t i, const float* albedo, const float* roughness, const float* wo,
+                                     const uint32_t* seed, uint8_t* ok, float* f_out, float* wi_out, float* pdf_out,
+                                     uint8_t* flags_out) {
+    fastlayer::Walk k;
+    const float3 o = v3(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]);
+    fastlayer::walk_begin_s(k, o, v3(albedo[3 * i], albedo[3 * i + 1], albedo[3 * i + 2]), roughness[i]);
+    const fastlayer::WalkKey key = fast_row_key(seed[i], i, (uint32_t)fastlayer::kWalks);
+    while (fastlayer::walk_step(k, key)) {}
+    const bool good = k.ok;
+    const float inv = good ? 1.0f / fabsf(k.w.z) : 0.0f;
+    ok[i] = good ? 1 : 0;
+    f_out[3 * i] = good ? k.beta.x * inv : 0.0f;
+    f_out[3 * i + 1] = good ? k.beta.y * inv : 0.0f;
+    f_out[3 * i + 2] = good ? k.beta.z * inv : 0.0f;
+    wi_out[3 * i] = good ? k.w.x : 0.0f;
+    wi_out[3 * i + 1] = good ? k.w.y : 0.0f;
+    wi_out[3 * i + 2] = good ? k.w.z : 0.0f;
+    pdf_out[i] = good ? 1.0f : 0.0f;
+    flags_out[i] = good ? (uint8_t)(o.z * k.w.z > 0.0f ? kLobeReflection : kLobeTransmission) : 0;
 }
 
 B2PT_HD void bsdf_row_pdf(int bsdf, int64_t i, const float* roughness, const float* wo, const float* wi,

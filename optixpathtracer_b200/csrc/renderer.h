@@ -43,6 +43,7 @@ struct B2ptRenderer {
     b2pt::DeviceBuffer<uint32_t> d_queues2;    // ... ordered by light visibility (K7p)
     b2pt::DeviceBuffer<uint32_t> d_counts;     // per-bounce counters
     b2pt::DeviceBuffer<float> d_wave_out;      // per-path radiance of the current wave (3 planes)
+    b2pt::DeviceBuffer<float> d_layered;       // scratch of the layered walk engine (shade_layered.cu), allocated on first use
     b2pt::DeviceBuffer<b2pt::TraceCounters> d_counters;
     b2pt::DeviceBuffer<float> d_frame;         // W*H*3 single-frame output (Render)
     b2pt::PathState st[2];

@@ -1,0 +1,305 @@
+// shade_layered.cu — K7d for the production (Philox) generator: the layered BSDF as a walk engine.
+//
+// Replaces, for rng_mode PHILOX, the serial k_shade<LAYERED> of wavefront.cu (which stays the kernel of the
+// bit-exact LCG modes): closest-hit part 2 of the reference (devicePrograms.cu:453-509) with
+// GlossyDiffuse::f / Sample_f (PBRT/GlossyDiffuse.h:141-367, :372-514) inside.  Three kernels per bounce:
+//
+//   K7d-p k_layered_prep    one thread per layered hit: local wo and light direction; hits whose light is visible
+//                           AND on wo's side of the shading normal are appended to the f list (f is exactly 0 for
+//                           the others)
+//   K7d-e k_layered_engine  persistent warps over WALK tasks (5 per f-list hit + 1 sample walk per hit), one
+//                           task per lane, refilled at step boundaries; per-lane logic in fast_layered.cuh
+//   K7d-f k_layered_finish  one thread per layered hit: entrance reflection + the five partial sums in walk
+//                           order (deterministic), NEE add, throughput, next ray, survivor compaction
+//
+// Built with --use_fast_math (see fast_layered.cuh for what that means for parity).
+#include <algorithm>
+#include <cstdlib>
+
+#include "bsdf_rows.cuh"
+#include "render.h"
+#include "wave_common.cuh"
+
+namespace b2pt {
+
+namespace {
+
+constexpr uint32_t kNoF = 0xffffffffu;
+
+// scratch of one bounce, `capacity` slots per plane (B2ptRenderer::d_layered)
+struct LayeredScratch {
+    float *wox, *woy, *woz;       // local outgoing direction, by slot
+    float *wlx, *wly, *wlz;       // local light direction, by slot (f-list hits only)
+    uint32_t* fidx;               // slot -> position in the f list, or kNoF
+    uint32_t* flist;              // f list: slots
+    float* fpart;                 // [walk][channel][f-list position]: 15 planes
+    float *swx, *swy, *swz;       // sample walk: direction (0,0,0 = no sample), by slot
+    float *sbx, *sby, *sbz;       // ... and weight f |cos| / pdf
+    uint32_t capacity;
+};
+constexpr int kLayeredScratchWords = 6 + 2 + 15 + 6;
+
+__device__ __forceinline__ fastlayer::WalkKey task_key(const WaveParams& wp, uint32_t id, uint32_t bounce, uint32_t walk) {
+    uint32_t pixel, sample;
+    path_identity(wp, id, pixel, sample);
+    fastlayer::WalkKey k;
+    k.k0 = (uint32_t)wp.seed ^ pixel;
+    k.k1 = (uint32_t)(wp.seed >> 32) ^ sample;
+    k.c1 = bounce | (fastlayer::kStageWalk << 16);
+    k.c2 = walk;
+    return k;
+}
+
+// ---- K7d-p -------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kWaveThreads)
+k_layered_prep(WaveParams wp, PathState st, SurfaceState sf, LayeredScratch ls, const uint32_t* __restrict__ lq,
+               const uint32_t* __restrict__ queued, uint32_t* __restrict__ lcounts, uint32_t bounce) {
+    const uint32_t n = queued[4 * bounce + kBsdfLayered];
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t iters = (n + stride - 1) / stride;
+    for (uint32_t it = 0; it < iters; it++) {
+        const uint32_t q = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        bool want_f = false;
+        uint32_t i = 0;
+        float3 wl = v3(0.0f);
+        if (q < n) {
+            i = lq[q];
+            const float3 ns = v3(sf.nx[i], sf.ny[i], sf.nz[i]);
+            float3 t, b;
+            tangent_frame(ns, t, b);
+            const float3 wo = to_local(t, b, ns, normalize(-v3(st.dx[i], st.dy[i], st.dz[i])));
+            ls.wox[i] = wo.x; ls.woy[i] = wo.y; ls.woz[i] = wo.z;
+            const uint32_t info = sf.info[i];
+            if ((info & kInfoHasLight) && (info & kInfoVisible)) {
+                const B2ptPointLight& L = wp.lights[info & 0xffu];
+                const float3 p = v3(sf.px[i], sf.py[i], sf.pz[i]);
+                wl = to_local(t, b, ns, normalize(v3(L.position[0], L.position[1], L.position[2]) - p));
+                want_f = wo.z * wl.z > 0.0f;
+            }
+        }
+        const uint32_t j = warp_append(want_f, lcounts);
+        if (want_f) {
+            ls.flist[j] = i;
+            ls.wlx[i] = wl.x; ls.wly[i] = wl.y; ls.wlz[i] = wl.z;
+        }
+        if (q < n) ls.fidx[i] = want_f ? j : kNoF;
+    }
+}
+
+// ---- K7d-e -------------------------------------------------------------------------------------
+// REFILL = idle lanes that trigger a task fetch.  A fetched lane starts at step 0 while its neighbours are
+// mid-walk; that costs nothing extra because every step has the same shape (fast_layered.cuh).
+template <int REFILL, int MINB>
+__global__ void __launch_bounds__(kWaveThreads, MINB)
+k_layered_engine(WaveParams wp, PathState st, SurfaceState sf, LayeredScratch ls, const uint32_t* __restrict__ lq,
+                 const uint32_t* __restrict__ queued, uint32_t* __restrict__ lcounts, uint32_t bounce) {
+    using namespace fastlayer;
+    const uint32_t n = queued[4 * bounce + kBsdfLayered];
+    const uint32_t n_f = lcounts[0];
+    const uint32_t n_tasks = (uint32_t)kWalks * n_f + n;
+    uint32_t* cursor = lcounts + 1;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t below = (1u << lane) - 1u;
+
+    Walk k;
+    k.step = -1;
+    WalkKey key = {0u, 0u, 0u, 0u};
+    uint32_t out = 0;            // f walk: f-list position; sample walk: slot
+    bool exhausted = false;      // warp-uniform
+    for (;;) {
+        const uint32_t idle = __ballot_sync(0xffffffffu, k.step < 0);
+        if (!exhausted && __popc(idle) >= REFILL) {
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(cursor, (uint32_t)__popc(idle));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            exhausted = base + (uint32_t)__popc(idle) >= n_tasks;
+            if (k.step < 0) {
+                const uint32_t t = base + (uint32_t)__popc(idle & below);
+                if (t < n_tasks) {
+                    const bool is_f = t < (uint32_t)kWalks * n_f;
+                    uint32_t i, walk;
+                    if (is_f) {                 // walk-major: neighbouring lanes take neighbouring hits
+                        walk = t / n_f;
+                        out = t - walk * n_f;
+                        i = ls.flist[out];
+                    } else {
+                        walk = (uint32_t)kWalks;
+                        i = lq[t - (uint32_t)kWalks * n_f];
+                        out = i;
+                    }
+                    const float3 wo = v3(ls.wox[i], ls.woy[i], ls.woz[i]);
+                    const float3 albedo = v3(sf.ar[i], sf.ag[i], sf.ab[i]);
+                    const float rough = sf.rough[i];
+                    key = task_key(wp, st.id[i], bounce, walk);
+                    if (is_f) walk_begin_f(k, wo, v3(ls.wlx[i], ls.wly[i], ls.wlz[i]), albedo, rough);
+                    else walk_begin_s(k, wo, albedo, rough);
+                }
+            }
+        }
+        if (__ballot_sync(0xffffffffu, k.step >= 0) == 0u) {
+            if (exhausted) break;
+            continue;
+        }
+        if (k.step >= 0 && !walk_step(k, key)) {
+            if (k.is_f) {
+                float* fp = ls.fpart + (size_t)key.c2 * 3u * ls.capacity + out;
+                fp[0] = k.f.x;
+                fp[ls.capacity] = k.f.y;
+                fp[2 * (size_t)ls.capacity] = k.f.z;
+            } else {
+                const float3 w = k.ok ? k.w : v3(0.0f);
+                ls.swx[out] = w.x; ls.swy[out] = w.y; ls.swz[out] = w.z;
+                ls.sbx[out] = k.beta.x; ls.sby[out] = k.beta.y; ls.sbz[out] = k.beta.z;
+            }
+        }
+    }
+}
+
+// ---- K7d-f -------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kWaveThreads)
+k_layered_finish(WaveParams wp, PathState st, PathState nx, SurfaceState sf, LayeredScratch ls,
+                 const uint32_t* __restrict__ lq, WaveCounts wc, uint32_t bounce, float* __restrict__ wave_out) {
+    const uint32_t n = wc.queued[4 * bounce + kBsdfLayered];
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t iters = (n + stride - 1) / stride;
+    for (uint32_t it = 0; it < iters; it++) {
+        const uint32_t q = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        bool alive = false;
+        float3 beta = v3(0.0f), radiance = v3(0.0f), next_o = v3(0.0f), next_d = v3(0.0f);
+        uint32_t id = 0;
+        if (q < n) {
+            const uint32_t i = lq[q];
+            id = st.id[i];
+            beta = v3(st.bx[i], st.by[i], st.bz[i]);
+            radiance = v3(st.rx[i], st.ry[i], st.rz[i]);
+            const float3 p = v3(sf.px[i], sf.py[i], sf.pz[i]);
+            const uint32_t j = ls.fidx[i];
+            if (j != kNoF) {   // NEE (devicePrograms.cu:453-472) with f = entrance reflection + mean of the five walks
+                float3 wo = v3(ls.wox[i], ls.woy[i], ls.woz[i]), wl = v3(ls.wlx[i], ls.wly[i], ls.wlz[i]);
+                const float cos_l = fabsf(wl.z);
+                if (wo.z < 0.0f) { wo = -wo; wl = -wl; }
+                const float rough = sf.rough[i];
+                float3 sum = v3(0.0f);
+#pragma unroll
+                for (int w = 0; w < fastlayer::kWalks; w++) {
+                    const float* fp = ls.fpart + (size_t)w * 3u * ls.capacity + j;
+                    sum += v3(fp[0], fp[ls.capacity], fp[2 * (size_t)ls.capacity]);
+                }
+                const float3 f = v3(fastlayer::entrance_reflection(wo, wl, rough * rough)) + sum * (1.0f / (float)fastlayer::kWalks);
+                const float3 spectrum = f * cos_l;
+                if (nonzero(spectrum)) {
+                    const uint32_t info = sf.info[i];
+                    const B2ptPointLight& L = wp.lights[info & 0xffu];
+                    const float p_light = wp.n_lights == 1 ? 1.0f : 1.0f / (float)wp.n_lights;
+                    const float3 dl = p - v3(L.position[0], L.position[1], L.position[2]);
+                    const float3 li = v3(L.color[0], L.color[1], L.color[2]) / dot(dl, dl);
+                    radiance += (beta * spectrum * li) / p_light;
+                }
+            }
+            const float3 wi = v3(ls.swx[i], ls.swy[i], ls.swz[i]);
+            if (wi.z != 0.0f) {   // GetNewRayDirection + throughput + next ray (:474-509)
+                beta *= v3(ls.sbx[i], ls.sby[i], ls.sbz[i]);
+                const float3 ns = v3(sf.nx[i], sf.ny[i], sf.nz[i]);
+                float3 t, b;
+                tangent_frame(ns, t, b);
+                float3 offset = 1e-3f * v3(sf.gx[i], sf.gy[i], sf.gz[i]);
+                if (wi.z < 0.0f) offset = -offset;
+                next_o = p + offset;
+                next_d = normalize(to_world(t, b, ns, wi));
+                alive = path_continues(beta, (int)bounce + 1, wp.max_bounces);
+            }
+            if (!alive) {
+                wave_out[id] = radiance.x;
+                wave_out[wp.capacity + id] = radiance.y;
+                wave_out[2 * wp.capacity + id] = radiance.z;
+            }
+        }
+        const uint32_t jn = warp_append(alive, wc.active + bounce + 1);
+        if (alive) {
+            nx.ox[jn] = next_o.x; nx.oy[jn] = next_o.y; nx.oz[jn] = next_o.z;
+            nx.dx[jn] = next_d.x; nx.dy[jn] = next_d.y; nx.dz[jn] = next_d.z;
+            nx.bx[jn] = beta.x; nx.by[jn] = beta.y; nx.bz[jn] = beta.z;
+            nx.rx[jn] = radiance.x; nx.ry[jn] = radiance.y; nx.rz[jn] = radiance.z;
+            nx.id[jn] = id;
+            nx.seed[jn] = 0u;
+        }
+    }
+}
+
+LayeredScratch scratch_view(B2ptRenderer* r, uint32_t capacity) {
+    r->d_layered.alloc((size_t)kLayeredScratchWords * capacity);
+    float* w = r->d_layered.get();
+    auto take = [&]() { float* p = w; w += capacity; return p; };
+    LayeredScratch ls;
+    ls.wox = take(); ls.woy = take(); ls.woz = take();
+    ls.wlx = take(); ls.wly = take(); ls.wlz = take();
+    ls.fidx = reinterpret_cast<uint32_t*>(take());
+    ls.flist = reinterpret_cast<uint32_t*>(take());
+    ls.fpart = w; w += (size_t)15 * capacity;
+    ls.swx = take(); ls.swy = take(); ls.swz = take();
+    ls.sbx = take(); ls.sby = take(); ls.sbz = take();
+    ls.capacity = capacity;
+    return ls;
+}
+
+// ---- rows for the parity hooks (b2pt_bsdf_f / b2pt_bsdf_sample with rng PHILOX) ---------------
+__global__ void k_fast_rows_f(int64_t n, const float* albedo, const float* roughness, const float* wo, const float* wi,
+                              const uint32_t* seed, float* f_out) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) fast_layered_row_f(i, albedo, roughness, wo, wi, seed, f_out);
+}
+__global__ void k_fast_rows_sample(int64_t n, const float* albedo, const float* roughness, const float* wo,
+                                   const uint32_t* seed, uint8_t* ok, float* f_out, float* wi_out, float* pdf_out,
+                                   uint8_t* flags_out) {
+    const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (i < n) fast_layered_row_sample(i, albedo, roughness, wo, seed, ok, f_out, wi_out, pdf_out, flags_out);
+}
+
+}  // namespace
+
+bool layered_engine_enabled() {
+    static const bool on = [] { const char* e = getenv("B2PT_LAYERED_ENGINE"); return !e || atoi(e) != 0; }();
+    return on;
+}
+
+size_t layered_scratch_bytes_per_path() { return (size_t)kLayeredScratchWords * 4; }
+
+// enqueue K7d-p, K7d-e, K7d-f for bounce b; returns the kernels launched
+int launch_layered_engine(B2ptRenderer* r, const WaveParams& wp, const PathState& cur, const PathState& nxt,
+                          const WaveCounts& wc, uint32_t* lcounts, uint32_t bounce) {
+    cudaStream_t s = r->stream;
+    const LayeredScratch ls = scratch_view(r, wp.capacity);
+    const uint32_t* lq = r->d_queues.get() + (size_t)kBsdfLayered * wp.capacity;
+    const int grid = r->sm_count * 8;
+    k_layered_prep<<<grid, kWaveThreads, 0, s>>>(wp, cur, r->surf, ls, lq, wc.queued, lcounts, bounce);
+    // A/B: B2PT_ENGINE_REFILL = idle lanes that trigger a fetch (1 | 4 | 8 | 16 | 32), B2PT_ENGINE_OCC = blocks per SM
+    static const int refill = [] { const char* e = getenv("B2PT_ENGINE_REFILL"); return e ? atoi(e) : 4; }();
+    static const int occ = [] { const char* e = getenv("B2PT_ENGINE_OCC"); return e ? atoi(e) : 6; }();
+#define B2PT_ENGINE(R, O) \
+    k_layered_engine<R, O><<<r->sm_count * O, kWaveThreads, 0, s>>>(wp, cur, r->surf, ls, lq, wc.queued, lcounts, bounce)
+    if (occ >= 8) {
+        if (refill >= 32) B2PT_ENGINE(32, 8); else if (refill >= 16) B2PT_ENGINE(16, 8); else if (refill >= 8) B2PT_ENGINE(8, 8);
+        else if (refill >= 4) B2PT_ENGINE(4, 8); else B2PT_ENGINE(1, 8);
+    } else if (occ >= 6) {
+        if (refill >= 32) B2PT_ENGINE(32, 6); else if (refill >= 16) B2PT_ENGINE(16, 6); else if (refill >= 8) B2PT_ENGINE(8, 6);
+        else if (refill >= 4) B2PT_ENGINE(4, 6); else B2PT_ENGINE(1, 6);
+    } else {
+        if (refill >= 32) B2PT_ENGINE(32, 4); else if (refill >= 16) B2PT_ENGINE(16, 4); else if (refill >= 8) B2PT_ENGINE(8, 4);
+        else if (refill >= 4) B2PT_ENGINE(4, 4); else B2PT_ENGINE(1, 4);
+    }
+#undef B2PT_ENGINE
+    k_layered_finish<<<grid, kWaveThreads, 0, s>>>(wp, cur, nxt, r->surf, ls, lq, wc, bounce, r->d_wave_out.get());
+    return 3;
+}
+
+void launch_fast_layered_rows_f(int64_t n, const float* albedo, const float* roughness, const float* wo, const float* wi,
+                                const uint32_t* seed, float* f_out) {
+    k_fast_rows_f<<<(unsigned)((n + 127) / 128), 128>>>(n, albedo, roughness, wo, wi, seed, f_out);
+}
+void launch_fast_layered_rows_sample(int64_t n, const float* albedo, const float* roughness, const float* wo,
+                                     const uint32_t* seed, uint8_t* ok, float* f_out, float* wi_out, float* pdf_out,
+                                     uint8_t* flags_out) {
+    k_fast_rows_sample<<<(unsigned)((n + 127) / 128), 128>>>(n, albedo, roughness, wo, seed, ok, f_out, wi_out, pdf_out, flags_out);
+}
+
+}  // namespace b2pt

@@ -1,0 +1,79 @@
+// wave_common.cuh — what the kernels of one wave share (wavefront.cu, shade_layered.cu):
+// the per-wave parameter block (the reference's LaunchParams, LaunchParams.h:9-29, cut to
+// what the stages read), the device-side counters, and the warp-aggregated queue append.
+#pragma once
+
+#include "integrator.cuh"
+#include "wavefront.cuh"
+
+struct B2ptRenderer;
+
+namespace b2pt {
+
+constexpr int kWaveThreads = 128;
+
+struct WaveParams {
+    CameraParams cam;
+    const B2ptPointLight* lights;
+    int32_t n_lights;
+    int32_t max_bounces;
+    int32_t mode;          // B2PT_BSDF_*
+    uint64_t seed;
+    uint32_t p0, np;       // pixel tile [p0, p0 + np)
+    uint32_t spw;          // samples in this wave
+    uint32_t frame0;       // frame.id of the wave's first sample
+    uint32_t capacity;     // slots per SoA array
+    int32_t cull_nee;      // 1: K6 drops shadow rays with a provably zero contribution
+    int32_t cull_layered;  // 1: ... also for the layered BSDF (only where skipping f leaves the random stream
+                           //    of the rest untouched: the Philox engine, shade_layered.cu)
+};
+
+// counters of one wave, zeroed before K4:  active[b] = rays traced at bounce b,
+// queued[b][k] = hits shaded with BSDF k at bounce b
+struct WaveCounts {
+    uint32_t* active;   // [max_bounces + 1]
+    uint32_t* queued;   // [max_bounces][4]
+};
+
+// layout of B2ptRenderer::d_counts (uint32 words); max_bounces <= 99 is enforced by b2pt_create / the setter
+constexpr int kCountsActive = 0;          // [100]
+constexpr int kCountsQueued = 100;        // [100][4]
+constexpr int kCountsPartition = 501;     // [100][4][2] K7p cursors (LCG modes)
+constexpr int kCountsLayered = 1301;      // [100][4]: f-hit count, task cursor, spare, spare (Philox engine)
+constexpr int kCountsWords = 1301 + 400;
+
+// ---- the layered walk engine (shade_layered.cu) ----------------------------------------------------
+// B2PT_LAYERED_ENGINE=0 sends the Philox mode through the serial k_shade<LAYERED> too (A/B, tests)
+bool layered_engine_enabled();
+size_t layered_scratch_bytes_per_path();
+// enqueue K7d-p/e/f of bounce `bounce` on r->stream; lcounts = 4 zeroed words; returns the kernels launched
+int launch_layered_engine(B2ptRenderer* r, const WaveParams& wp, const PathState& cur, const PathState& nxt,
+                          const WaveCounts& wc, uint32_t* lcounts, uint32_t bounce);
+// parity-hook rows of the engine's per-lane logic (device pointers, default stream)
+void launch_fast_layered_rows_f(int64_t n, const float* albedo, const float* roughness, const float* wo, const float* wi,
+                                const uint32_t* seed, float* f_out);
+void launch_fast_layered_rows_sample(int64_t n, const float* albedo, const float* roughness, const float* wo,
+                                     const uint32_t* seed, uint8_t* ok, float* f_out, float* wi_out, float* pdf_out,
+                                     uint8_t* flags_out);
+
+#if defined(__CUDACC__)
+__device__ __forceinline__ void path_identity(const WaveParams& wp, uint32_t id, uint32_t& pixel, uint32_t& sample) {
+    const uint32_t s_local = id / wp.np;
+    pixel = wp.p0 + (id - s_local * wp.np);
+    sample = wp.frame0 + s_local;
+}
+
+// warp-aggregated append: every lane of the warp must call this
+__device__ __forceinline__ uint32_t warp_append(bool want, uint32_t* counter) {
+    const uint32_t mask = __ballot_sync(0xffffffffu, want);
+    if (mask == 0u) return 0u;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return base + (uint32_t)__popc(mask & ((1u << lane) - 1u));
+}
+#endif
+
+}  // namespace b2pt

@@ -23,43 +23,17 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <type_traits>
 
 #include "render.h"
-#include "integrator.cuh"
 #include "traverse.cuh"
+#include "wave_common.cuh"
 
 namespace b2pt {
 
 namespace {
 
-constexpr int kThreads = 128;
-
-struct WaveParams {
-    CameraParams cam;
-    const B2ptPointLight* lights;
-    int32_t n_lights;
-    int32_t max_bounces;
-    int32_t mode;          // B2PT_BSDF_*
-    uint64_t seed;
-    uint32_t p0, np;       // pixel tile [p0, p0 + np)
-    uint32_t spw;          // samples in this wave
-    uint32_t frame0;       // frame.id of the wave's first sample
-    uint32_t capacity;     // slots per SoA array
-    int32_t cull_nee;      // 1: K6 drops shadow rays with a provably zero contribution (B2PT_CULL_NEE=0 disables)
-};
-
-// counters of one wave, zeroed before K4:  active[b] = rays traced at bounce b,
-// queued[b][k] = hits shaded with BSDF k at bounce b
-struct WaveCounts {
-    uint32_t* active;   // [max_bounces + 1]
-    uint32_t* queued;   // [max_bounces][4]
-};
-
-__device__ __forceinline__ void path_identity(const WaveParams& wp, uint32_t id, uint32_t& pixel, uint32_t& sample) {
-    const uint32_t s_local = id / wp.np;
-    pixel = wp.p0 + (id - s_local * wp.np);
-    sample = wp.frame0 + s_local;
-}
+constexpr int kThreads = kWaveThreads;
 
 // ---- K4 ----------------------------------------------------------------------
 template <class Rng>
@@ -80,18 +54,6 @@ k_raygen(WaveParams wp, PathState st, uint32_t* __restrict__ active0) {
         st.id[i] = i;
         st.seed[i] = RngIO<Rng>::first_state(pixel, sample);
     }
-}
-
-// warp-aggregated append: every lane of the warp must call this
-__device__ __forceinline__ uint32_t warp_append(bool want, uint32_t* counter) {
-    const uint32_t mask = __ballot_sync(0xffffffffu, want);
-    if (mask == 0u) return 0u;
-    const int lane = threadIdx.x & 31;
-    const int leader = __ffs(mask) - 1;
-    uint32_t base = 0;
-    if (lane == leader) base = atomicAdd(counter, (uint32_t)__popc(mask));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    return base + (uint32_t)__popc(mask & ((1u << lane) - 1u));
 }
 
 // ---- K6 ----------------------------------------------------------------------
@@ -154,13 +116,16 @@ k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restri
                 // so whether it runs must follow the reference.  Output bits are unchanged; the counter
                 // `shadow_rays` keeps the reference's count, `shadow_rays_traced` is what K8 really ran.
                 bool trace_shadow = s.sh_tmax >= 0.0f;
-                if (trace_shadow && kind != kBsdfLayered) {
+                if (trace_shadow && (kind != kBsdfLayered || wp.cull_layered)) {
                     const float3 ray_d = v3(st.dx[i], st.dy[i], st.dz[i]);
                     const float wo_z = dot(s.ns, normalize(-ray_d)), wl_z = dot(s.ns, s.sh_d);
                     const bool smooth = effectively_smooth(roughness_to_alpha(s.sp.roughness));
                     const bool opposite = !(wo_z * wl_z > 0.0f);   // !same_hemisphere(wo, wl)
+                    // layered (walk engine only, where skipping f does not shift the random stream of the sample): every
+                    // walk of f ends at the opaque base when the light is on the other side — exactly 0 (fast_layered.cuh)
                     const bool zero_f = kind == kBsdfConductor ? (smooth || opposite)
                                       : kind == kBsdfDiffuse   ? opposite
+                                      : kind == kBsdfLayered   ? opposite
                                                                : smooth;   // dielectric
                     if (zero_f && wp.cull_nee) {
                         trace_shadow = false;
@@ -354,7 +319,7 @@ void layout_wave(B2ptRenderer* r, uint32_t capacity) {
     r->d_queues.alloc((size_t)4 * capacity);
     r->d_queues2.alloc((size_t)4 * capacity);
     r->d_wave_out.alloc((size_t)3 * capacity);
-    r->d_counts.alloc((size_t)5 * 100 + 1 + 8 * 100);   // active[<=100] + queued[<=99][4] + partition cursors[<=100][4][2]
+    r->d_counts.alloc((size_t)kCountsWords);   // wave_common.cuh: active, queued, K7p cursors, walk-engine counters
     float* w = r->d_words.get();
     auto take = [&]() { float* p = w; w += capacity; return p; };
     for (int k = 0; k < 2; k++) {
@@ -386,8 +351,8 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
     const int grid = r->sm_count * 8;
     const DeviceScene sc = r->scene.view();
     WaveCounts wc;
-    wc.active = r->d_counts.get();
-    wc.queued = r->d_counts.get() + 100;
+    wc.active = r->d_counts.get() + kCountsActive;
+    wc.queued = r->d_counts.get() + kCountsQueued;
     LaunchCfg lc;
     lc.stream = s;
     lc.grid = r->sm_count * trace_grid_blocks_per_sm();
@@ -415,76 +380,45 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
     mark(kClsOther);
     const bool kinds[4] = {wp.mode == B2PT_BSDF_AUTO || wp.mode == B2PT_BSDF_CONDUCTOR, wp.mode == B2PT_BSDF_DIFFUSE,
                            wp.mode == B2PT_BSDF_DIELECTRIC, wp.mode == B2PT_BSDF_AUTO || wp.mode == B2PT_BSDF_LAYERED};
+    // the layered BSDF with the production generator runs as a walk engine (shade_layered.cu); the LCG modes — whose
+    // draws must come in the reference's order — run the serial kernel below, visible hits first (K7p)
+    const bool engine = std::is_same<Rng, PhiloxRng>::value && kinds[3] && layered_engine_enabled();
     for (int b = 0; b < wp.max_bounces; b++) {
         const PathState& cur = r->st[b & 1];
         const PathState& nxt = r->st[(b + 1) & 1];
         launch_closest(lc, sc, cur, wc.active + b, 0.0f, 100.0f, r->d_hits.get(), r->d_counters.get(), /*finish=*/false);   // tmin 0, tmax 100 (:652)
         mark(kClsClosest);
-        // K6 waits on gathers (triangle, normals, material): A/B of resident blocks per SM, B2PT_SURF_OCC = 8 | 10 | 12
-        static const int socc = [] { const char* e = getenv("B2PT_SURF_OCC"); return e ? atoi(e) : 8; }();
-        if (socc >= 12)
-            k_surface<Rng, 12><<<r->sm_count * 12, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
-                                                                   wc, (uint32_t)b, r->d_wave_out.get(), r->d_counters.get());
-        else if (socc >= 10)
-            k_surface<Rng, 10><<<r->sm_count * 10, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
-                                                                   wc, (uint32_t)b, r->d_wave_out.get(), r->d_counters.get());
-        else
-            k_surface<Rng><<<grid, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
-                                                     wc, (uint32_t)b, r->d_wave_out.get(), r->d_counters.get());
+        k_surface<Rng><<<grid, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
+                                                 wc, (uint32_t)b, r->d_wave_out.get(), r->d_counters.get());
         count();
         mark(kClsSurface);
         if (wp.n_lights > 0) {
             launch_any(lc, sc, r->shadow, wc.active + b, 0.0f, r->surf.info, nullptr, r->d_counters.get());
             mark(kClsAny);
         }
-        uint32_t* q = r->d_queues.get();
+        const uint32_t* q = r->d_queues.get();
         const size_t cap = wp.capacity;
-        static const int partition = [] { const char* e = getenv("B2PT_PARTITION"); return e ? atoi(e) : 1; }();
-        uint32_t* q3 = q;   // the layered queue K7d reads
-        if (wp.n_lights > 0 && partition == 2) {          // K7p over all four queues (A/B only)
-            k_partition_queues<<<dim3((unsigned)(r->sm_count * 4), 4), 256, 0, s>>>(
-                r->d_queues.get(), r->d_queues2.get(), r->surf.info, wc, (uint32_t)b, wp.capacity,
-                r->d_counts.get() + 501 + 8 * b, 0u);
-            count();
+        // 8 resident blocks per SM (64 registers, a few spilled words) beat 6 (80 registers) for all shade kernels:
+        // they are bound by instruction issue / fetch, not by registers (profiles/r01_ab_shade_occupancy.txt)
+        const int g3 = r->sm_count * 16;
+        if (kinds[0]) { k_shade<kBsdfConductor, Rng, 8><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 0 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+        if (kinds[1]) { k_shade<kBsdfDiffuse, Rng, 8><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 1 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+        if (kinds[2]) { k_shade<kBsdfDielectric, Rng, 8><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 2 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
+        if (kinds[3] && engine) {
+            count(launch_layered_engine(r, wp, cur, nxt, wc, r->d_counts.get() + kCountsLayered + 4 * b, (uint32_t)b));
+            r->launches_kernel_cls[kClsShade] += 2;
             mark(kClsShade);
-            q = q3 = r->d_queues2.get();
-        } else if (wp.n_lights > 0 && partition == 1 && kinds[3]) {   // K7p: visible hits first in the layered queue
-            k_partition_queues<<<dim3((unsigned)(r->sm_count * 4), 1), 256, 0, s>>>(
-                r->d_queues.get(), r->d_queues2.get(), r->surf.info, wc, (uint32_t)b, wp.capacity,
-                r->d_counts.get() + 501 + 8 * b, 3u);
-            count();
-            mark(kClsShade);
-            q3 = r->d_queues2.get();
-        }
-        // resident blocks per SM of the three lighter shade kernels: 8 (64 registers, a few spilled words) beats 6
-        // (80 registers) — they are bound by instruction issue with 24 warps per SM; c2 513 -> 536, c3 426 -> 449
-        // Msamples/s (A/B: B2PT_SHADE_OCC3 = 6 | 8)
-        static const int occ3 = [] { const char* e = getenv("B2PT_SHADE_OCC3"); return e ? atoi(e) : 8; }();
-        const int g3 = r->sm_count * (occ3 >= 8 ? 16 : 8);
-        if (occ3 >= 8) {
-            if (kinds[0]) { k_shade<kBsdfConductor, Rng, 8><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 0 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
-            if (kinds[1]) { k_shade<kBsdfDiffuse, Rng, 8><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 1 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
-            if (kinds[2]) { k_shade<kBsdfDielectric, Rng, 8><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 2 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
-        } else {
-            if (kinds[0]) { k_shade<kBsdfConductor, Rng><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 0 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
-            if (kinds[1]) { k_shade<kBsdfDiffuse, Rng><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 1 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
-            if (kinds[2]) { k_shade<kBsdfDielectric, Rng><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 2 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
-        }
-        if (kinds[3]) {
-            // the layered kernel waits on instruction fetch (4 500 instructions, twice the instruction cache):
-            // more resident warps hide it better than more registers per thread help (A/B: B2PT_SHADE_OCC)
-            static const int occ = [] { const char* e = getenv("B2PT_SHADE_OCC"); return e ? atoi(e) : 8; }();
-            const int g = r->sm_count * std::max(occ, 4) * 2;
-            if (occ >= 12)
-                k_shade<kBsdfLayered, Rng, 12><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
-            else if (occ >= 10)
-                k_shade<kBsdfLayered, Rng, 10><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
-            else if (occ >= 8)
-                k_shade<kBsdfLayered, Rng, 8><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
-            else if (occ >= 6)
-                k_shade<kBsdfLayered, Rng, 6><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
-            else
-                k_shade<kBsdfLayered, Rng, 4><<<g, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
+        } else if (kinds[3]) {
+            const uint32_t* q3 = q;
+            if (wp.n_lights > 0) {   // K7p: visible hits first in the layered queue
+                k_partition_queues<<<dim3((unsigned)(r->sm_count * 4), 1), 256, 0, s>>>(
+                    r->d_queues.get(), r->d_queues2.get(), r->surf.info, wc, (uint32_t)b, wp.capacity,
+                    r->d_counts.get() + kCountsPartition + 8 * b, 3u);
+                count();
+                mark(kClsShade);
+                q3 = r->d_queues2.get();
+            }
+            k_shade<kBsdfLayered, Rng, 8><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q3 + 3 * cap, wc, (uint32_t)b, r->d_wave_out.get());
             count();
             mark(kClsShade);
         }
@@ -513,7 +447,8 @@ void render_frames(B2ptRenderer* r, int spp, bool accumulate) {
         const uint64_t want = n_pixels * (uint64_t)std::max(spp, 1);
         log2cap = 20;
         while ((1ull << log2cap) < want && log2cap < 26) log2cap++;
-        const size_t per_path = (size_t)(2 * kPathStateWords + kSurfaceStateWords + kShadowWords) * 4 + sizeof(HitRecord) + 32 + 12;
+        const size_t per_path = (size_t)(2 * kPathStateWords + kSurfaceStateWords + kShadowWords) * 4 + sizeof(HitRecord) + 32 + 12 +
+                                layered_scratch_bytes_per_path();
         const size_t held = r->d_hits.size();                      // paths the buffers hold now
         if (((size_t)1 << log2cap) > held) {                       // growing: never more than half of the free memory
             size_t free_b = 0, total_b = 0;                        // (asked only now: cudaMemGetInfo can take tens of ms
@@ -541,6 +476,7 @@ void render_frames(B2ptRenderer* r, int spp, bool accumulate) {
     wp.capacity = capacity;
     static const int cull_nee = [] { const char* e = getenv("B2PT_CULL_NEE"); return e ? atoi(e) : 1; }();
     wp.cull_nee = cull_nee;
+    wp.cull_layered = cull_nee && r->cfg.rng_mode == B2PT_RNG_PHILOX && layered_engine_enabled();
     float* dst = accumulate ? r->d_accum.get() : r->d_frame.get();
 
     r->timing_used = 0;

@@ -190,7 +190,10 @@ void hostsim_bsdf_f(int bsdf, int lcg_mode, int64_t n, const float* albedo, cons
                     const float* wo, const float* wi, const uint32_t* seed, float* f_out, uint32_t* seed_out) {
 #pragma omp parallel for schedule(static)
     for (int64_t i = 0; i < n; i++) {
-        if (lcg_mode == B2PT_RNG_LCG_HOST)
+        if (lcg_mode == B2PT_RNG_PHILOX) {   // the production walk engine (layered only)
+            fast_layered_row_f(i, albedo, roughness, wo, wi, seed, f_out);
+            if (seed_out) seed_out[i] = 0u;
+        } else if (lcg_mode == B2PT_RNG_LCG_HOST)
             bsdf_row_f<LcgRng<true>>(bsdf, i, albedo, roughness, wo, wi, seed, f_out, seed_out);
         else
             bsdf_row_f<LcgRng<false>>(bsdf, i, albedo, roughness, wo, wi, seed, f_out, seed_out);
@@ -202,7 +205,10 @@ void hostsim_bsdf_sample(int bsdf, int lcg_mode, int64_t n, const float* albedo,
                          float* pdf_out, uint8_t* flags_out, uint32_t* seed_out) {
 #pragma omp parallel for schedule(static)
     for (int64_t i = 0; i < n; i++) {
-        if (lcg_mode == B2PT_RNG_LCG_HOST)
+        if (lcg_mode == B2PT_RNG_PHILOX) {
+            fast_layered_row_sample(i, albedo, roughness, wo, seed, ok, f_out, wi_out, pdf_out, flags_out);
+            if (seed_out) seed_out[i] = 0u;
+        } else if (lcg_mode == B2PT_RNG_LCG_HOST)
             bsdf_row_sample<LcgRng<true>>(bsdf, i, albedo, roughness, wo, seed, ok, f_out, wi_out, pdf_out,
                                           flags_out, seed_out);
         else

@@ -53,6 +53,14 @@ def test_argument_checks_without_a_device():
     assert lib.b2pt_create(None, None, C.byref(h)) == -1            # null scene
     assert lib.b2pt_resize(None, 4, 4) == -1 and lib.b2pt_render(None, None) == -1
     lib.b2pt_destroy(None)                                          # no-op
+    # b2pt_create validates the config with the setters' ranges before it touches a device
+    scene = _lib.B2ptSceneDesc()
+    for field, bad in (("max_bounces", 100), ("max_bounces", -1), ("bsdf_mode", 5), ("bsdf_mode", -1), ("rng_mode", 3),
+                       ("wave_paths_log2", 5), ("wave_paths_log2", 28), ("bvh_leaf_size", 9)):
+        lib.b2pt_default_config(C.byref(cfg))
+        setattr(cfg, field, bad)
+        assert lib.b2pt_create(C.byref(scene), C.byref(cfg), C.byref(h)) == -1, (field, bad)
+        assert not h.value and field.split("_")[0] in lib.b2pt_last_error(None).decode()
 
 
 def test_cpp_shim_compiles():

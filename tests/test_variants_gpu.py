@@ -1,7 +1,7 @@
 """GPU tier: every A/B build variant of the traversal kernels gives the same bits.
 
 The switches (B2PT_STEP, B2PT_TRIQ, B2PT_BVH4, B2PT_DEFER, B2PT_TRAVERSAL, B2PT_SMALL_CHUNKS, B2PT_COLLAPSE, and the
-shading-side B2PT_PARTITION, B2PT_SHADE_OCC*, B2PT_SURF_OCC, B2PT_CULL_NEE) are
+shading-side B2PT_CULL_NEE, B2PT_ENGINE_REFILL, B2PT_ENGINE_OCC — how the layered walk engine hands tasks to lanes) are
 read once per process, so each variant runs in its own subprocess (tests/variant_probe.py): closest hits must
 equal the fp64 brute-force oracle bit for bit, and the occlusion answers, a frame in the reference's random
 sequence and an accumulated Philox image must be identical across variants — and across wave capacities."""
@@ -31,9 +31,8 @@ VARIANTS = {
     "thread_per_ray": {"B2PT_TRAVERSAL": "0"},
     "fixed_collapse_big_chunks": {"B2PT_COLLAPSE": "fixed", "B2PT_SMALL_CHUNKS": "0"},
     "occupancy_8": {"B2PT_OCC": "8"},
-    "shade_queues_in_arrival_order": {"B2PT_PARTITION": "0"},
-    "all_shade_queues_by_visibility": {"B2PT_PARTITION": "2"},
-    "shade_and_surface_occupancy": {"B2PT_SHADE_OCC": "6", "B2PT_SHADE_OCC3": "6", "B2PT_SURF_OCC": "10"},
+    "walk_engine_refills_every_idle_lane": {"B2PT_ENGINE_REFILL": "1", "B2PT_ENGINE_OCC": "8"},
+    "walk_engine_refills_whole_warps": {"B2PT_ENGINE_REFILL": "32", "B2PT_ENGINE_OCC": "4"},
     "every_shadow_ray_traced": {"B2PT_CULL_NEE": "0"},
     "any_hit_nearest_first_break_20": {"B2PT_ANY_UNSORTED": "0", "B2PT_BREAK": "20"},
 }
