@@ -236,8 +236,31 @@ def load_gltf(path, compat: bool = False) -> dict:
     return {"meshes": meshes, "textures": textures, "lights": lights, "camera": camera}
 
 
-def save_gltf(scene: dict, path, embed: bool = False):
-    """Write a scene dict as glTF 2.0: `path`.gltf + .bin (+ PNG textures), or everything inline."""
+def _decompose_trs(model):
+    """translation, rotation (x, y, z, w), scale of an affine matrix without shear (T * R * S)."""
+    m = np.asarray(model, dtype=np.float64).reshape(4, 4)
+    t = m[:3, 3]
+    s = np.linalg.norm(m[:3, :3], axis=0)
+    if np.linalg.det(m[:3, :3]) < 0:
+        s[0] = -s[0]
+    r = m[:3, :3] / np.where(s == 0, 1.0, s)
+    if not np.allclose(r.T @ r, np.eye(3), atol=1e-5):
+        raise GltfError("compat: the model matrix has shear; the reference loader reads translation / rotation / scale only")
+    w = np.sqrt(max(0.0, 1.0 + r[0, 0] + r[1, 1] + r[2, 2])) / 2.0
+    if w > 1e-6:
+        q = [(r[2, 1] - r[1, 2]) / (4 * w), (r[0, 2] - r[2, 0]) / (4 * w), (r[1, 0] - r[0, 1]) / (4 * w), w]
+    else:   # rotation by pi: the axis is the eigenvector of eigenvalue 1
+        ev, evec = np.linalg.eigh((r + r.T) / 2)
+        ax = evec[:, np.argmax(ev)]
+        q = [ax[0], ax[1], ax[2], 0.0]
+    return t.tolist(), [float(v) for v in q], s.tolist()
+
+
+def save_gltf(scene: dict, path, embed: bool = False, compat: bool = False):
+    """Write a scene dict as glTF 2.0: `path`.gltf + .bin (+ PNG textures), or everything inline.
+    compat=True writes what the reference's loader can read (ModelLoading/ModelLoader.cpp:91-245): node transforms
+    as translation / rotation / scale (it ignores `matrix`), u16 indices, and no mesh-less root nodes (it
+    dereferences node.mesh of every root: the lights stay in the file but out of the scene's roots)."""
     from PIL import Image
     import io
     path = Path(path)
@@ -268,7 +291,9 @@ def save_gltf(scene: dict, path, embed: bool = False):
         if m.get("texcoords") is not None:
             att["TEXCOORD_0"] = add(m["texcoords"].astype(f32), 34962)
         idx = np.asarray(m["indices"]).reshape(-1)
-        idx = idx.astype(np.uint16) if len(m["positions"]) <= 65535 else idx.astype(np.uint32)
+        if compat and len(m["positions"]) > 65536:
+            raise GltfError("compat: the reference loader reads 16-bit indices only (ModelLoader.cpp:145)")
+        idx = idx.astype(np.uint16) if len(m["positions"]) <= 65536 else idx.astype(np.uint32)
         prim = {"attributes": att, "indices": add(idx, 34963), "material": len(materials)}
         pbr = {"baseColorFactor": [float(c) for c in m["albedo"]] + [1.0], "metallicFactor": float(m["metallic"]),
                "roughnessFactor": float(m["roughness"])}
@@ -283,7 +308,11 @@ def save_gltf(scene: dict, path, embed: bool = False):
         materials.append(mat)
         meshes.append({"primitives": [prim], "name": m.get("name", "mesh")})
         model = np.asarray(m.get("model", np.eye(4)), dtype=np.float64).reshape(4, 4)
-        nodes.append({"mesh": len(meshes) - 1, "name": m.get("name", "mesh"), "matrix": model.T.reshape(16).tolist()})
+        if compat:
+            t, q, sc = _decompose_trs(model)
+            nodes.append({"mesh": len(meshes) - 1, "name": m.get("name", "mesh"), "translation": t, "rotation": q, "scale": sc})
+        else:
+            nodes.append({"mesh": len(meshes) - 1, "name": m.get("name", "mesh"), "matrix": model.T.reshape(16).tolist()})
 
     j = {"asset": {"version": "2.0", "generator": "optixpathtracer_b200.gltf"}, "scene": 0,
          "scenes": [{"nodes": list(range(len(nodes)))}], "nodes": nodes, "meshes": meshes, "materials": materials,
@@ -311,7 +340,8 @@ def save_gltf(scene: dict, path, embed: bool = False):
             defs.append({"type": "point", "color": (col / inten).tolist(), "intensity": inten})
             j["nodes"].append({"name": f"light{len(defs) - 1}", "translation": [float(v) for v in pos],
                                "extensions": {"KHR_lights_punctual": {"light": len(defs) - 1}}})
-            j["scenes"][0]["nodes"].append(len(j["nodes"]) - 1)
+            if not compat:
+                j["scenes"][0]["nodes"].append(len(j["nodes"]) - 1)
         j["extensions"] = {"KHR_lights_punctual": {"lights": defs}}
     if embed:
         j["buffers"] = [{"byteLength": len(blob),

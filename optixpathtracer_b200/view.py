@@ -25,6 +25,7 @@ class OptixView:
         self.maxSamples = int(max_samples)
         self.samples = 0
         self.clearFrameBuffer = False
+        self.clearedToWhite = False   # a camera move clears the framebuffer with glClearColor(1, 1, 1, 1) (OptixView.cpp:144-146)
         self.camera = camera
         self.viewSize = tuple(int(v) for v in view_size)
         self.finished_exr = finished_exr
@@ -54,6 +55,7 @@ class OptixView:
     def Resize(self, width, height=None):
         self.viewSize = tuple(width) if height is None else (int(width), int(height))
         self.optixRenderer.Resize(self.viewSize)   # a new size starts a new image
+        self.clearedToWhite = False
         self.samples = 0
 
     # -- one iteration of OptixView::Run (OptixView.cpp:132-185) ------------------------
@@ -65,6 +67,7 @@ class OptixView:
             if self.clearFrameBuffer:          # the frame about to be rendered becomes sample 1 (:141-151)
                 self.clearFrameBuffer = False
                 r.ClearAccumulation()
+                self.clearedToWhite = True
                 self.samples = 0
             r.RenderAccumulate(1, download=False)   # DrawOptix + AddNewFrameToBuffer, on the device
             self.samples += 1
@@ -92,15 +95,16 @@ class OptixView:
         sum / maxSamples (AddPathtracedFrame.frag:18-24)."""
         s, n = self.optixRenderer.DownloadAccumulation()
         if self.maxSamples < 0:
-            return s / f32(max(n, 1))
-        return s / f32(self.maxSamples)
+            return s / f32(max(n, 1))       # mix(fb, new, 1 / samples): the first frame after a clear overwrites the white
+        # fb + new / maxSamples adds to whatever the clear left: white after a camera move (the reference's quirk, kept)
+        return s / f32(self.maxSamples) + (f32(1.0) if self.clearedToWhite else f32(0.0))
 
     # -- checkpoint / resume -------------------------------------------------------------
     def Save(self, path):
         s, n = self.optixRenderer.DownloadAccumulation()
         np.savez(Path(path), sum=s, samples=np.int64(self.samples), spp=np.int64(n),
                  frame_id=np.int64(self.optixRenderer.GetFrameId()), size=np.asarray(self.viewSize),
-                 position=self.camera.position, rotation=self.camera.rotation)
+                 position=self.camera.position, rotation=self.camera.rotation, white=np.bool_(self.clearedToWhite))
 
     def Load(self, path):
         z = np.load(Path(path))
@@ -110,6 +114,7 @@ class OptixView:
         self.optixRenderer.UploadAccumulation(z["sum"], int(z["spp"]))
         self.optixRenderer.SetFrameId(int(z["frame_id"]))
         self.samples = int(z["samples"])
+        self.clearedToWhite = bool(z["white"]) if "white" in z else False
         self.clearFrameBuffer = False
 
     def close(self):

@@ -288,3 +288,71 @@ class RefOracle:
         d = np.empty((width * height, 3), f32)
         self.lib.ref_camera_rays(C.c_int(width), C.c_int(height), fp(pos), fp(iv), fp(ip), fp(o), fp(d))
         return o, d
+
+
+class RefHost:
+    """oracle/_ref/libref_host.so: the reference's own HOST code compiled in place (oracle/ref_host.cpp) —
+    ModelLoader.cpp + Mesh.cpp (glTF ingestion, N1), WriteImage.cpp (BMP / EXR writers, N3), Camera.cpp."""
+
+    PATH = ROOT / "oracle" / "_ref" / "libref_host.so"
+
+    @classmethod
+    def available(cls) -> bool:
+        return cls.PATH.exists()
+
+    def __init__(self):
+        self.lib = C.CDLL(str(self.PATH))
+        self.lib.refhost_load_model.restype = C.c_void_p
+
+    def load_model(self, path) -> dict:
+        """ModelLoader::LoadModel(folder, file) -> the scene dict the product's loaders return."""
+        from pathlib import Path as P
+        p = P(path)
+        h = C.c_void_p(self.lib.refhost_load_model(str(p.parent).encode() + b"/", p.name.encode()))
+        try:
+            nm, nt = C.c_int(), C.c_int()
+            self.lib.refhost_model_counts(h, C.byref(nm), C.byref(nt))
+            meshes, textures = [], []
+            for i in range(nm.value):
+                nv, ntri, nuv = C.c_int(), C.c_int(), C.c_int()
+                model = np.empty(16, f32); albedo = np.empty(3, f32)
+                met, rough = C.c_float(), C.c_float()
+                tex = (C.c_int * 3)()
+                self.lib.refhost_mesh_info(h, i, C.byref(nv), C.byref(ntri), C.byref(nuv), fp(model), fp(albedo),
+                                           C.byref(met), C.byref(rough), tex)
+                pos = np.empty((nv.value, 3), f32); nrm = np.empty((nv.value, 3), f32)
+                uv = np.empty((nuv.value, 2), f32); idx = np.empty((ntri.value, 3), np.int32)
+                self.lib.refhost_mesh_arrays(h, i, fp(pos), fp(nrm), fp(uv), vp(idx))
+                meshes.append({"positions": pos, "normals": nrm, "texcoords": uv, "indices": idx,
+                               "model": model.reshape(4, 4).T.copy(), "albedo": albedo, "metallic": met.value,
+                               "roughness": rough.value, "tex_albedo": tex[0], "tex_normal": tex[1],
+                               "tex_metal_rough": tex[2]})
+            for i in range(nt.value):
+                w, hh = C.c_int(), C.c_int()
+                self.lib.refhost_texture_info(h, i, C.byref(w), C.byref(hh))
+                px = np.empty((hh.value, w.value, 4), np.uint8)
+                self.lib.refhost_texture_pixels(h, i, vp(px))
+                textures.append(px)
+        finally:
+            self.lib.refhost_model_free(h)
+        return {"meshes": meshes, "textures": textures}
+
+    def write_exr(self, rgb, path):
+        a = np.ascontiguousarray(rgb, dtype=f32)
+        self.lib.refhost_write_exr(fp(a), a.shape[1], a.shape[0], str(path).encode())
+
+    def write_bmp(self, rgb, path):
+        a = np.ascontiguousarray(rgb, dtype=f32)
+        self.lib.refhost_write_bmp(fp(a), a.shape[1], a.shape[0], str(path).encode())
+
+    def camera(self, blender_pos, blender_rot, fov_deg, aspect):
+        bp = np.ascontiguousarray(blender_pos, f32); br = np.ascontiguousarray(blender_rot, f32)
+        pos = np.empty(3, f32); view = np.empty(16, f32); proj = np.empty(16, f32)
+        self.lib.refhost_camera(fp(bp), fp(br), C.c_float(fov_deg), C.c_float(aspect), fp(pos), fp(view), fp(proj))
+        return pos, view, proj
+
+    def camera_engine(self, pos, rot, fov_deg, aspect):
+        p = np.ascontiguousarray(pos, f32); r = np.ascontiguousarray(rot, f32)
+        view = np.empty(16, f32); proj = np.empty(16, f32)
+        self.lib.refhost_camera_engine(fp(p), fp(r), C.c_float(fov_deg), C.c_float(aspect), fp(view), fp(proj))
+        return view, proj
