@@ -75,16 +75,18 @@ B2PT_HD fastlayer::WalkKey fast_row_key(uint32_t seed, int64_t i, uint32_t walk)
 // f = entrance reflection + (sum of the five walks) / 5; exactly 0 across the surface
 B2PT_HD float3 fast_layered_f(float3 albedo, float roughness, float3 wo, float3 wi, uint32_t seed, int64_t row) {
     if (!(wo.z * wi.z > 0.0f)) return v3(0.0f);
+    const float alpha = roughness * roughness;
+    const float lam_wi = fastlayer::walk_lambda_wi(wi, alpha);
     float3 sum = v3(0.0f);
     for (int w = 0; w < fastlayer::kWalks; w++) {
         fastlayer::Walk k;
-        fastlayer::walk_begin_f(k, wo, wi, albedo, roughness);
+        fastlayer::walk_begin_f(k, wo, wi, albedo, alpha, lam_wi);
         const fastlayer::WalkKey key = fast_row_key(seed, row, (uint32_t)w);
         while (fastlayer::walk_step(k, key)) {}
         sum += k.f;
     }
     fastlayer::Walk k0;
-    fastlayer::walk_begin_f(k0, wo, wi, albedo, roughness);
+    fastlayer::walk_begin_f(k0, wo, wi, albedo, alpha, lam_wi);
     return v3(fastlayer::entrance_reflection(k0.wo, k0.wi, k0.alpha)) + sum * (1.0f / (float)fastlayer::kWalks);
 }
 B2PT_HD void fast_layered_row_f(int64_t i, const float* albedo, const float* roughness, const float* wo, const float* wi,
@@ -102,7 +104,7 @@ B2PT_HD void fast_layered_row_sample(int64_t i, const float* albedo, const float
                                      uint8_t* flags_out) {
     fastlayer::Walk k;
     const float3 o = v3(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]);
-    fastlayer::walk_begin_s(k, o, v3(albedo[3 * i], albedo[3 * i + 1], albedo[3 * i + 2]), roughness[i]);
+    fastlayer::walk_begin_s(k, o, v3(albedo[3 * i], albedo[3 * i + 1], albedo[3 * i + 2]), roughness[i] * roughness[i]);
     const fastlayer::WalkKey key = fast_row_key(seed[i], i, (uint32_t)fastlayer::kWalks);
     while (fastlayer::walk_step(k, key)) {}
     const bool good = k.ok;

@@ -197,33 +197,34 @@ B2PT_HD void top_sample(float3 wo, float alpha, bool allow_r, bool allow_t, bool
         l1o = lambda1p(wo, a2);
         if (want_pdf) d = ggx_d(wm, a2);
     }
-    if (uc < pr / p_sum) {
-        const float3 wi = smooth ? v3(-wo.x, -wo.y, wo.z) : -wo + (2.0f * c) * wm;
-        if (!(wo.z * wi.z > 0.0f)) return;
-        float g_ratio = 1.0f;                   // G(wo, wi) / G1(wo)
-        if (!smooth) g_ratio = l1o / (l1o + lambda1p(wi, a2) - 1.0f);
-        s.wi = wi;
-        s.weight = g_ratio * p_sum;
-        s.reflected = true;
-        if (want_pdf) s.pdf = smooth ? pr / p_sum : d / (l1o * 4.0f * fabsf(wo.z)) * pr / p_sum;
+    // one tail for both lobes (a warp whose lanes sit in different walk phases runs it once): direction, the
+    // hemisphere test of that lobe, G / G1, the lobe's extra factor
+    const bool refl = uc < pr / p_sum;
+    float etap = 1.0f;
+    float3 wi = v3(0.0f, 0.0f, 1.0f);
+    bool good;
+    if (refl) {
+        wi = smooth ? v3(-wo.x, -wo.y, wo.z) : -wo + (2.0f * c) * wm;
+        good = wo.z * wi.z > 0.0f;
     } else {
-        float etap;
-        float3 wi;
-        if (!refract_about(wo, wm, etap, wi)) return;
-        if (wo.z * wi.z > 0.0f || wi.z == 0.0f) return;
-        float g_ratio = 1.0f;
-        if (!smooth) g_ratio = l1o / (l1o + lambda1p(wi, a2) - 1.0f);
-        s.wi = wi;
-        s.weight = g_ratio * p_sum;
-        if (radiance) s.weight /= etap * etap;
-        if (want_pdf) {
-            if (smooth) {
-                s.pdf = pt / p_sum;
-            } else {
-                const float dwi = dot(wi, wm);
-                const float sq = dwi + c / etap;
-                s.pdf = d / (l1o * fabsf(wo.z)) * fabsf(c) * fabsf(dwi) / (sq * sq) * pt / p_sum;
-            }
+        good = refract_about(wo, wm, etap, wi) && !(wo.z * wi.z > 0.0f) && wi.z != 0.0f;
+    }
+    if (!good) return;
+    float g_ratio = 1.0f;                       // G(wo, wi) / G1(wo)
+    if (!smooth) g_ratio = l1o / (l1o + lambda1p(wi, a2) - 1.0f);
+    s.wi = wi;
+    s.reflected = refl;
+    s.weight = g_ratio * p_sum;
+    if (!refl && radiance) s.weight /= etap * etap;
+    if (want_pdf) {
+        if (smooth) {
+            s.pdf = (refl ? pr : pt) / p_sum;
+        } else if (refl) {
+            s.pdf = d / (l1o * 4.0f * fabsf(wo.z)) * pr / p_sum;
+        } else {
+            const float dwi = dot(wi, wm);
+            const float sq = dwi + c / etap;
+            s.pdf = d / (l1o * fabsf(wo.z)) * fabsf(c) * fabsf(dwi) / (sq * sq) * pt / p_sum;
         }
     }
     s.ok = s.weight > 0.0f && s.wi.z != 0.0f;   // usable(): f != 0, pdf != 0, wi.z != 0 (NaN fails the first test)
@@ -296,7 +297,11 @@ struct Walk {
     bool flipped;      // wo.z was negative
 };
 
-B2PT_HD void walk_begin_f(Walk& k, float3 wo, float3 wi, float3 albedo, float roughness) {
+// Lambda(wi) of an f walk's light direction: per hit, not per walk (the engine's prep kernel stores it)
+B2PT_HD float walk_lambda_wi(float3 wi, float alpha) {
+    return alpha < 1e-3f ? 0.0f : lambda1p(wi, alpha * alpha) - 1.0f;
+}
+B2PT_HD void walk_begin_f(Walk& k, float3 wo, float3 wi, float3 albedo, float alpha, float lam_wi) {
     k.flipped = wo.z < 0.0f;
     if (k.flipped) {   // two-sided (:153-157)
         wo = -wo;
@@ -305,8 +310,8 @@ B2PT_HD void walk_begin_f(Walk& k, float3 wo, float3 wi, float3 albedo, float ro
     k.wo = wo;
     k.wi = wi;
     k.albedo = albedo;
-    k.alpha = roughness * roughness;   // Surface.h:26
-    k.lam_wi = k.alpha < 1e-3f ? 0.0f : lambda1p(wi, k.alpha * k.alpha) - 1.0f;
+    k.alpha = alpha;   // roughness^2, Surface.h:26
+    k.lam_wi = lam_wi;
     k.w = v3(0.0f, 0.0f, -1.0f);
     k.beta = k.f = v3(0.0f);
     k.c_wis = 0.0f;
@@ -314,13 +319,13 @@ B2PT_HD void walk_begin_f(Walk& k, float3 wo, float3 wi, float3 albedo, float ro
     k.is_f = true;
     k.ok = false;
 }
-B2PT_HD void walk_begin_s(Walk& k, float3 wo, float3 albedo, float roughness) {
+B2PT_HD void walk_begin_s(Walk& k, float3 wo, float3 albedo, float alpha) {
     k.flipped = wo.z < 0.0f;
     if (k.flipped) wo = -wo;
     k.wo = wo;
     k.wi = v3(0.0f, 0.0f, 1.0f);
     k.albedo = albedo;
-    k.alpha = roughness * roughness;
+    k.alpha = alpha;
     k.lam_wi = 0.0f;
     k.w = v3(0.0f, 0.0f, -1.0f);
     k.beta = k.f = v3(0.0f);

@@ -27,9 +27,15 @@ namespace {
 constexpr uint32_t kNoF = 0xffffffffu;
 
 // scratch of one bounce, `capacity` slots per plane (B2ptRenderer::d_layered)
+// task record of one hit, 64 bytes, written by K7d-p and read by every walk task of the hit (the five f walks of
+// a hit sit in neighbouring lanes and share the loads):
+//   q[0] = local wo, alpha      q[1] = albedo, Philox key word 0
+//   q[2] = local light direction, Lambda(wl)  (f-list hits only)      q[3] = Philox key word 1
+struct alignas(16) HitTask {
+    float4 q[4];
+};
 struct LayeredScratch {
-    float *wox, *woy, *woz;       // local outgoing direction, by slot
-    float *wlx, *wly, *wlz;       // local light direction, by slot (f-list hits only)
+    HitTask* task;                // by slot
     uint32_t* fidx;               // slot -> position in the f list, or kNoF
     uint32_t* flist;              // f list: slots
     float* fpart;                 // [walk][channel][f-list position]: 15 planes
@@ -37,7 +43,7 @@ struct LayeredScratch {
     float *sbx, *sby, *sbz;       // ... and weight f |cos| / pdf
     uint32_t capacity;
 };
-constexpr int kLayeredScratchWords = 6 + 2 + 15 + 6;
+constexpr int kLayeredScratchWords = 16 + 2 + 15 + 6;
 
 __device__ __forceinline__ fastlayer::WalkKey task_key(const WaveParams& wp, uint32_t id, uint32_t bounce, uint32_t walk) {
     uint32_t pixel, sample;
@@ -62,13 +68,20 @@ k_layered_prep(WaveParams wp, PathState st, SurfaceState sf, LayeredScratch ls, 
         bool want_f = false;
         uint32_t i = 0;
         float3 wl = v3(0.0f);
+        float3 wo = v3(0.0f);
+        float alpha = 0.0f;
         if (q < n) {
             i = lq[q];
             const float3 ns = v3(sf.nx[i], sf.ny[i], sf.nz[i]);
             float3 t, b;
             tangent_frame(ns, t, b);
-            const float3 wo = to_local(t, b, ns, normalize(-v3(st.dx[i], st.dy[i], st.dz[i])));
-            ls.wox[i] = wo.x; ls.woy[i] = wo.y; ls.woz[i] = wo.z;
+            wo = to_local(t, b, ns, normalize(-v3(st.dx[i], st.dy[i], st.dz[i])));
+            const float rough = sf.rough[i];
+            alpha = rough * rough;                       // Surface.h:26
+            const fastlayer::WalkKey key = task_key(wp, st.id[i], bounce, 0u);
+            ls.task[i].q[0] = make_float4(wo.x, wo.y, wo.z, alpha);
+            ls.task[i].q[1] = make_float4(sf.ar[i], sf.ag[i], sf.ab[i], __uint_as_float(key.k0));
+            ls.task[i].q[3] = make_float4(__uint_as_float(key.k1), 0.0f, 0.0f, 0.0f);
             const uint32_t info = sf.info[i];
             if ((info & kInfoHasLight) && (info & kInfoVisible)) {
                 const B2ptPointLight& L = wp.lights[info & 0xffu];
@@ -80,7 +93,7 @@ k_layered_prep(WaveParams wp, PathState st, SurfaceState sf, LayeredScratch ls, 
         const uint32_t j = warp_append(want_f, lcounts);
         if (want_f) {
             ls.flist[j] = i;
-            ls.wlx[i] = wl.x; ls.wly[i] = wl.y; ls.wlz[i] = wl.z;
+            ls.task[i].q[2] = make_float4(wl.x, wl.y, wl.z, fastlayer::walk_lambda_wi(wo.z < 0.0f ? -wl : wl, alpha));
         }
         if (q < n) ls.fidx[i] = want_f ? j : kNoF;
     }
@@ -91,8 +104,8 @@ k_layered_prep(WaveParams wp, PathState st, SurfaceState sf, LayeredScratch ls, 
 // mid-walk; that costs nothing extra because every step has the same shape (fast_layered.cuh).
 template <int REFILL, int MINB>
 __global__ void __launch_bounds__(kWaveThreads, MINB)
-k_layered_engine(WaveParams wp, PathState st, SurfaceState sf, LayeredScratch ls, const uint32_t* __restrict__ lq,
-                 const uint32_t* __restrict__ queued, uint32_t* __restrict__ lcounts, uint32_t bounce) {
+k_layered_engine(LayeredScratch ls, const uint32_t* __restrict__ lq, const uint32_t* __restrict__ queued,
+                 uint32_t* __restrict__ lcounts, uint32_t bounce) {
     using namespace fastlayer;
     const uint32_t n = queued[4 * bounce + kBsdfLayered];
     const uint32_t n_f = lcounts[0];
@@ -118,21 +131,27 @@ k_layered_engine(WaveParams wp, PathState st, SurfaceState sf, LayeredScratch ls
                 if (t < n_tasks) {
                     const bool is_f = t < (uint32_t)kWalks * n_f;
                     uint32_t i, walk;
-                    if (is_f) {                 // walk-major: neighbouring lanes take neighbouring hits
-                        walk = t / n_f;
-                        out = t - walk * n_f;
+                    if (is_f) {                 // walk-minor: the five walks of a hit sit in neighbouring lanes
+                        out = t / (uint32_t)kWalks;
+                        walk = t - out * (uint32_t)kWalks;
                         i = ls.flist[out];
                     } else {
                         walk = (uint32_t)kWalks;
                         i = lq[t - (uint32_t)kWalks * n_f];
                         out = i;
                     }
-                    const float3 wo = v3(ls.wox[i], ls.woy[i], ls.woz[i]);
-                    const float3 albedo = v3(sf.ar[i], sf.ag[i], sf.ab[i]);
-                    const float rough = sf.rough[i];
-                    key = task_key(wp, st.id[i], bounce, walk);
-                    if (is_f) walk_begin_f(k, wo, v3(ls.wlx[i], ls.wly[i], ls.wlz[i]), albedo, rough);
-                    else walk_begin_s(k, wo, albedo, rough);
+                    const float4* rec = ls.task[i].q;
+                    const float4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q3 = __ldg(rec + 3);
+                    key.k0 = __float_as_uint(q1.w);
+                    key.k1 = __float_as_uint(q3.x);
+                    key.c1 = bounce | (kStageWalk << 16);
+                    key.c2 = walk;
+                    if (is_f) {
+                        const float4 q2 = __ldg(rec + 2);
+                        walk_begin_f(k, v3(q0.x, q0.y, q0.z), v3(q2.x, q2.y, q2.z), v3(q1.x, q1.y, q1.z), q0.w, q2.w);
+                    } else {
+                        walk_begin_s(k, v3(q0.x, q0.y, q0.z), v3(q1.x, q1.y, q1.z), q0.w);
+                    }
                 }
             }
         }
@@ -175,17 +194,17 @@ k_layered_finish(WaveParams wp, PathState st, PathState nx, SurfaceState sf, Lay
             const float3 p = v3(sf.px[i], sf.py[i], sf.pz[i]);
             const uint32_t j = ls.fidx[i];
             if (j != kNoF) {   // NEE (devicePrograms.cu:453-472) with f = entrance reflection + mean of the five walks
-                float3 wo = v3(ls.wox[i], ls.woy[i], ls.woz[i]), wl = v3(ls.wlx[i], ls.wly[i], ls.wlz[i]);
+                const float4 q0 = ls.task[i].q[0], q2 = ls.task[i].q[2];
+                float3 wo = v3(q0.x, q0.y, q0.z), wl = v3(q2.x, q2.y, q2.z);
                 const float cos_l = fabsf(wl.z);
                 if (wo.z < 0.0f) { wo = -wo; wl = -wl; }
-                const float rough = sf.rough[i];
                 float3 sum = v3(0.0f);
 #pragma unroll
                 for (int w = 0; w < fastlayer::kWalks; w++) {
                     const float* fp = ls.fpart + (size_t)w * 3u * ls.capacity + j;
                     sum += v3(fp[0], fp[ls.capacity], fp[2 * (size_t)ls.capacity]);
                 }
-                const float3 f = v3(fastlayer::entrance_reflection(wo, wl, rough * rough)) + sum * (1.0f / (float)fastlayer::kWalks);
+                const float3 f = v3(fastlayer::entrance_reflection(wo, wl, q0.w)) + sum * (1.0f / (float)fastlayer::kWalks);
                 const float3 spectrum = f * cos_l;
                 if (nonzero(spectrum)) {
                     const uint32_t info = sf.info[i];
@@ -231,8 +250,7 @@ LayeredScratch scratch_view(B2ptRenderer* r, uint32_t capacity) {
     float* w = r->d_layered.get();
     auto take = [&]() { float* p = w; w += capacity; return p; };
     LayeredScratch ls;
-    ls.wox = take(); ls.woy = take(); ls.woz = take();
-    ls.wlx = take(); ls.wly = take(); ls.wlz = take();
+    ls.task = reinterpret_cast<HitTask*>(w); w += (size_t)16 * capacity;
     ls.fidx = reinterpret_cast<uint32_t*>(take());
     ls.flist = reinterpret_cast<uint32_t*>(take());
     ls.fpart = w; w += (size_t)15 * capacity;
@@ -273,10 +291,10 @@ int launch_layered_engine(B2ptRenderer* r, const WaveParams& wp, const PathState
     const int grid = r->sm_count * 8;
     k_layered_prep<<<grid, kWaveThreads, 0, s>>>(wp, cur, r->surf, ls, lq, wc.queued, lcounts, bounce);
     // A/B: B2PT_ENGINE_REFILL = idle lanes that trigger a fetch (1 | 4 | 8 | 16 | 32), B2PT_ENGINE_OCC = blocks per SM
-    static const int refill = [] { const char* e = getenv("B2PT_ENGINE_REFILL"); return e ? atoi(e) : 4; }();
+    static const int refill = [] { const char* e = getenv("B2PT_ENGINE_REFILL"); return e ? atoi(e) : 32; }();
     static const int occ = [] { const char* e = getenv("B2PT_ENGINE_OCC"); return e ? atoi(e) : 6; }();
 #define B2PT_ENGINE(R, O) \
-    k_layered_engine<R, O><<<r->sm_count * O, kWaveThreads, 0, s>>>(wp, cur, r->surf, ls, lq, wc.queued, lcounts, bounce)
+    k_layered_engine<R, O><<<r->sm_count * O, kWaveThreads, 0, s>>>(ls, lq, wc.queued, lcounts, bounce)
     if (occ >= 8) {
         if (refill >= 32) B2PT_ENGINE(32, 8); else if (refill >= 16) B2PT_ENGINE(16, 8); else if (refill >= 8) B2PT_ENGINE(8, 8);
         else if (refill >= 4) B2PT_ENGINE(4, 8); else B2PT_ENGINE(1, 8);

@@ -104,7 +104,7 @@ def test_c5_terrain_closest_and_any_hits_match_the_brute_force(terrain):
         op, ot, ou, ov, _ = oracle.closest(soup, o, d)
         assert np.array_equal(gp, op), f"{(gp != op).sum()} primitive ids differ"
         assert np.array_equal(bits(gt), bits(ot)) and np.array_equal(bits(gu), bits(ou)) and np.array_equal(bits(gv), bits(ov))
-        assert (op >= 0).mean() > 0.5          # the rays do hit the scene
+        assert (op >= 0).mean() > 0.3          # the rays do hit the scene
         # occlusion towards C5's lights from the hit points (LightVisibility, devicePrograms.cu:216-241)
         hit = op >= 0
         p = (o[hit].astype(np.float64) + d[hit].astype(np.float64) * ot[hit, None]).astype(f32)
