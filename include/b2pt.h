@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define B2PT_ABI_VERSION 3
+#define B2PT_ABI_VERSION 4
 
 /* ---- status codes ------------------------------------------------------ */
 enum {
@@ -240,6 +240,56 @@ int b2pt_write_exr(B2ptRenderer* r, const char* path);
 int b2pt_set_kernel_timing(B2ptRenderer* r, int32_t on);
 int b2pt_get_stats(const B2ptRenderer* r, B2ptStats* out);
 int b2pt_reset_stats(B2ptRenderer* r);
+
+/* ---- multi-GPU -------------------------------------------- *
+ * The reference renders on device 0 only (OptixRenderer.cpp:70).  Here the path
+ * shards by SAMPLES: every device renders a disjoint range of the absolute sample
+ * indices (the Philox key holds the absolute index, so the union is the 1-GPU
+ * image up to fp32 re-association), scene + BVH are replicated, and the W*H*3
+ * fp32 sums are combined once per call.
+ *
+ * (a) ONE process, N devices.  b2pt_create_multi builds one renderer per device
+ *     (concurrently); the b2pt_multi_* setters broadcast; b2pt_multi_renderer gives
+ *     the per-device handle for everything else (stats, per-device settings).
+ *     b2pt_multi_render_accumulate splits `spp_total` over the devices, renders on
+ *     one host thread per device, and sums the buffers with ONE kernel on
+ *     devices[0] that reads its peers' memory over NVLink (device order, so the
+ *     result is deterministic), scales by 1 / spp and downloads.               */
+typedef struct B2ptMulti B2ptMulti;
+int  b2pt_create_multi(const int32_t* devices, int32_t n_devices, const B2ptSceneDesc* scene,
+                       const B2ptConfig* cfg /* .device ignored */, B2ptMulti** out);
+void b2pt_destroy_multi(B2ptMulti* m);
+const char* b2pt_multi_last_error(const B2ptMulti* m);
+int32_t b2pt_multi_device_count(const B2ptMulti* m);
+B2ptRenderer* b2pt_multi_renderer(B2ptMulti* m, int32_t i);
+int b2pt_multi_resize(B2ptMulti* m, int32_t width, int32_t height);
+int b2pt_multi_set_camera(B2ptMulti* m, const float position[3],
+                          const float inverse_view[16], const float inverse_projection[16]);
+int b2pt_multi_set_lights(B2ptMulti* m, const B2ptPointLight* lights, int32_t n_lights);
+int b2pt_multi_set_max_bounces(B2ptMulti* m, int32_t max_bounces);
+int b2pt_multi_set_bsdf_mode(B2ptMulti* m, int32_t bsdf_mode);
+int b2pt_multi_set_rng(B2ptMulti* m, int32_t rng_mode, uint64_t seed);
+int b2pt_multi_set_frame_id(B2ptMulti* m, uint32_t frame_id);
+int b2pt_multi_clear_accumulation(B2ptMulti* m);
+int b2pt_multi_render_accumulate(B2ptMulti* m, int32_t spp_total, float* h_rgb_mean);
+
+/* (b) one process PER device (torchrun / MPI).  Rank 0 calls b2pt_dist_unique_id,
+ *     the host program hands the 128 bytes to every rank (torch.distributed
+ *     broadcast, MPI_Bcast, a file ...), every rank calls b2pt_dist_init on its own
+ *     renderer (created with B2ptConfig.device = its GPU).  Then
+ *     b2pt_dist_render_accumulate is a COLLECTIVE: this rank traces `spp` further
+ *     samples starting at its own frame id (give the ranks disjoint ranges with
+ *     b2pt_set_frame_id), the accumulation buffers are summed on rank 0 with one
+ *     ncclReduce(sum, fp32, W*H*3) on the renderer's stream straight out of the
+ *     buffer K9 wrote, and rank 0's h_rgb_mean (may be NULL; ignored elsewhere)
+ *     receives sum / (samples accumulated over all ranks since their last clear).
+ *     NCCL (libnccl.so.2) is dlopen'ed by the first b2pt_dist_* call; the library
+ *     loads and renders without it.                                            */
+#define B2PT_DIST_ID_BYTES 128
+int b2pt_dist_unique_id(uint8_t id[B2PT_DIST_ID_BYTES]);
+int b2pt_dist_init(B2ptRenderer* r, const uint8_t id[B2PT_DIST_ID_BYTES], int32_t rank, int32_t world);
+int b2pt_dist_render_accumulate(B2ptRenderer* r, int32_t spp, float* h_rgb_mean);
+int b2pt_dist_shutdown(B2ptRenderer* r);
 
 /* ---- parity hooks (the same kernels the renderer launches) ------------- */
 /* optixTrace(..., RADIANCE ...) (devicePrograms.cu:248): closest hit of n

@@ -12,6 +12,9 @@ def __getattr__(name):
     if name == "OptixRenderer":
         from .api import OptixRenderer
         return OptixRenderer
+    if name == "MultiRenderer":
+        from .api import MultiRenderer
+        return MultiRenderer
     if name == "OptixView":
         from .view import OptixView
         return OptixView

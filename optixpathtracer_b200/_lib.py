@@ -111,6 +111,26 @@ SIGNATURES = {
     "b2pt_bsdf_pdf": (C.c_int, [C.c_int32, C.c_int32, C.c_int64, c_float_p, c_float_p, c_float_p,
                                  C.c_int32, C.c_int32, c_float_p]),
     "b2pt_download_bvh": (C.c_int, [_H, C.c_void_p, c_int32_p]),
+    # multi-GPU, one process (csrc/multi.cu)
+    "b2pt_create_multi": (C.c_int, [c_int32_p, C.c_int32, C.POINTER(B2ptSceneDesc), C.POINTER(B2ptConfig), C.POINTER(_H)]),
+    "b2pt_destroy_multi": (None, [_H]),
+    "b2pt_multi_last_error": (C.c_char_p, [_H]),
+    "b2pt_multi_device_count": (C.c_int32, [_H]),
+    "b2pt_multi_renderer": (_H, [_H, C.c_int32]),
+    "b2pt_multi_resize": (C.c_int, [_H, C.c_int32, C.c_int32]),
+    "b2pt_multi_set_camera": (C.c_int, [_H, c_float_p, c_float_p, c_float_p]),
+    "b2pt_multi_set_lights": (C.c_int, [_H, C.POINTER(B2ptPointLight), C.c_int32]),
+    "b2pt_multi_set_max_bounces": (C.c_int, [_H, C.c_int32]),
+    "b2pt_multi_set_bsdf_mode": (C.c_int, [_H, C.c_int32]),
+    "b2pt_multi_set_rng": (C.c_int, [_H, C.c_int32, C.c_uint64]),
+    "b2pt_multi_set_frame_id": (C.c_int, [_H, C.c_uint32]),
+    "b2pt_multi_clear_accumulation": (C.c_int, [_H]),
+    "b2pt_multi_render_accumulate": (C.c_int, [_H, C.c_int32, c_float_p]),
+    # multi-GPU, one process per device (NCCL)
+    "b2pt_dist_unique_id": (C.c_int, [c_uint8_p]),
+    "b2pt_dist_init": (C.c_int, [_H, c_uint8_p, C.c_int32, C.c_int32]),
+    "b2pt_dist_render_accumulate": (C.c_int, [_H, C.c_int32, c_float_p]),
+    "b2pt_dist_shutdown": (C.c_int, [_H]),
 }
 
 _lib = None

@@ -229,6 +229,29 @@ class OptixRenderer:
     def ResetStats(self):
         check(self._h, self.lib.b2pt_reset_stats(self._h))
 
+    # -- one process per GPU: NCCL reduce inside the library (csrc/multi.cu) -------------
+    @staticmethod
+    def DistUniqueId() -> np.ndarray:
+        """128 bytes from rank 0 that every rank passes to DistInit (broadcast them with whatever the host has)."""
+        idb = np.zeros(128, dtype=np.uint8)
+        rc = _lib.load().b2pt_dist_unique_id(idb.ctypes.data_as(_lib.c_uint8_p))
+        if rc != 0:
+            check(None, rc)
+        return idb
+
+    def DistInit(self, unique_id: np.ndarray, rank: int, world: int):
+        idb = np.ascontiguousarray(unique_id, dtype=np.uint8)
+        assert idb.size == 128
+        check(self._h, self.lib.b2pt_dist_init(self._h, idb.ctypes.data_as(_lib.c_uint8_p), int(rank), int(world)))
+
+    def DistRenderAccumulate(self, spp: int, out: np.ndarray | None = None):
+        """Collective: every rank traces `spp` samples from its own frame id; rank 0's `out` receives the mean."""
+        check(self._h, self.lib.b2pt_dist_render_accumulate(self._h, int(spp), _fp(out) if out is not None else None))
+        return out
+
+    def DistShutdown(self):
+        check(self._h, self.lib.b2pt_dist_shutdown(self._h))
+
     # -- parity hooks -------------------------------------------------------
     def TraceClosest(self, org, dirs, tmin: float = 0.0, tmax: float = 100.0):
         o = np.ascontiguousarray(org, dtype=f32).reshape(-1, 3)
@@ -263,3 +286,95 @@ class OptixRenderer:
         check(self._h, self.lib.b2pt_download_bvh(self._h, nodes.ctypes.data_as(C.c_void_p),
                                                   order.ctypes.data_as(_lib.c_int32_p)))
         return nodes, order
+
+
+class MultiRenderer:
+    """One process, several GPUs (b2pt_create_multi): the samples of a call are split over the devices and the
+    sums are combined by one kernel on devices[0] reading its peers over NVLink.  Same method names as
+    OptixRenderer for the reference surface; `renderer(i)` wraps device i's handle for everything else."""
+
+    def __init__(self, model: dict, devices, *, bsdf_mode="auto", rng_mode="philox", seed: int = 0x5EED,
+                 max_bounces: int = 8, wave_paths_log2: int = 0):
+        self.lib = _lib.load()
+        cfg = B2ptConfig()
+        self.lib.b2pt_default_config(C.byref(cfg))
+        cfg.bsdf_mode = BSDF_NAMES[bsdf_mode] if isinstance(bsdf_mode, str) else int(bsdf_mode)
+        cfg.rng_mode = RNG_NAMES[rng_mode] if isinstance(rng_mode, str) else int(rng_mode)
+        cfg.seed = seed
+        cfg.max_bounces = max_bounces
+        cfg.wave_paths_log2 = wave_paths_log2
+        marshal = _SceneMarshal(model)
+        dev = np.ascontiguousarray(devices, dtype=np.int32)
+        h = C.c_void_p()
+        rc = self.lib.b2pt_create_multi(dev.ctypes.data_as(_lib.c_int32_p), len(dev), C.byref(marshal.desc), C.byref(cfg), C.byref(h))
+        if rc != 0:
+            msg = self.lib.b2pt_multi_last_error(None)
+            raise _lib.B2ptError(rc, msg.decode() if msg else "")
+        self._h = h
+        self.devices = [int(d) for d in dev]
+        self.width = self.height = 0
+
+    def _check(self, rc):
+        if rc != 0:
+            msg = self.lib.b2pt_multi_last_error(self._h)
+            raise _lib.B2ptError(rc, msg.decode() if msg else "")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self.lib.b2pt_destroy_multi(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def Resize(self, new_size):
+        w, h = int(new_size[0]), int(new_size[1])
+        self._check(self.lib.b2pt_multi_resize(self._h, w, h))
+        if w and h:
+            self.width, self.height = w, h
+
+    def SetCamera(self, camera):
+        pos, iv, ip = camera.launch_matrices(self.width, self.height)
+        self._check(self.lib.b2pt_multi_set_camera(self._h, _fp(np.ascontiguousarray(pos, f32)), _fp(np.ascontiguousarray(iv, f32)),
+                                                   _fp(np.ascontiguousarray(ip, f32))))
+
+    def SetLights(self, lights):
+        arr = (B2ptPointLight * max(len(lights), 1))()
+        for i, (p, c) in enumerate(lights):
+            arr[i].position = (C.c_float * 3)(*np.asarray(p, dtype=f32))
+            arr[i].color = (C.c_float * 3)(*np.asarray(c, dtype=f32))
+        self._check(self.lib.b2pt_multi_set_lights(self._h, arr, len(lights)))
+
+    def SetMaxBounces(self, n: int):
+        self._check(self.lib.b2pt_multi_set_max_bounces(self._h, int(n)))
+
+    def SetFrameId(self, frame_id: int):
+        self._check(self.lib.b2pt_multi_set_frame_id(self._h, int(frame_id)))
+
+    def ClearAccumulation(self):
+        self._check(self.lib.b2pt_multi_clear_accumulation(self._h))
+
+    def RenderAccumulate(self, spp_total: int, out: np.ndarray | None = None, download: bool = True):
+        if download and out is None:
+            out = np.empty((self.height, self.width, 3), dtype=f32)
+        self._check(self.lib.b2pt_multi_render_accumulate(self._h, int(spp_total), _fp(out) if download else None))
+        return out if download else None
+
+    def renderer(self, i: int) -> "OptixRenderer":
+        """Device i's renderer as a borrowed OptixRenderer (stats, per-device settings); do not close it."""
+        r = OptixRenderer.__new__(OptixRenderer)
+        r.lib = self.lib
+        r.model = None
+        r._h = C.c_void_p(self.lib.b2pt_multi_renderer(self._h, int(i)))
+        r.close = lambda: None          # the handle belongs to the MultiRenderer
+        r.width, r.height = self.width, self.height
+        return r

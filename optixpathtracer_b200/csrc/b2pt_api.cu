@@ -115,6 +115,7 @@ void b2pt_destroy(B2ptRenderer* r) {
     if (!r) return;
     cudaSetDevice(r->device);
     if (r->stream) cudaStreamSynchronize(r->stream);
+    if (r->dist_comm) b2pt_dist_shutdown(r);
     r->scene.free_textures();
     for (cudaEvent_t e : r->timing_events) cudaEventDestroy(e);
     if (r->ev0) cudaEventDestroy(r->ev0);

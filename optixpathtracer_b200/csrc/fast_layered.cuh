@@ -338,98 +338,92 @@ B2PT_HD void walk_begin_s(Walk& k, float3 wo, float3 albedo, float alpha) {
 // Russian roulette of both walk kinds (:230-247, :424-437): only past depth 3, only below 1/4
 B2PT_HD bool walk_roulette(Walk& k, const WalkKey& key, int depth, int which) {
     const float m = max3(k.beta);
+    bool survive = true;
     if (depth > 3 && m < 0.25f) {
         const float q = fmaxf(0.0f, 1.0f - m);
-        if (walk_rr_uniform(key, k.step, which) < q) return false;
+        survive = !(walk_rr_uniform(key, k.step, which) < q);
         k.beta = k.beta * (1.0f / (1.0f - q));
     }
-    return true;
+    return survive;
 }
 
 // One step = [top event][bottom event].  Returns false when the task is finished:
 //   f walk:      k.f is this walk's contribution to 5 f (the caller adds the entrance reflection and divides)
 //   sample walk: k.ok, and on success k.w = sampled direction (un-flipped), k.beta = f |cos| / pdf
+//
+// Control flow is kept STRUCTURED on purpose — one `alive` flag, no return before the end: a warp of the engine
+// holds walks of both kinds in different steps, and an early return inside a conditional moves the point where
+// its lanes meet again to the end of the function, so that the two heavy blocks (the visible-normal sample of
+// the top event, the next-event term of the bottom event) would run once per GROUP of lanes instead of once per
+// warp (measured: 11.9 active lanes per instruction instead of 20, profiles/r02_k_layered_engine_*).
 B2PT_HD bool walk_step(Walk& k, const WalkKey& key) {
     const int st = k.step;
     const Draws u = walk_draws(key, st);
     const bool smooth = k.alpha < 1e-3f;
     const float a2 = k.alpha * k.alpha;
+    const bool is_f = k.is_f;
+    const bool first = st == 0;
+    const bool pre_b = is_f && st == 1;                 // the f walk's pre-sample of wis
+    const bool walking = st >= (is_f ? 2 : 1);          // a top event of the walk proper
 
     // ---- top ----
-    float3 dir;
-    bool allow_r, allow_t, radiance = true, want_pdf = false, pre;
-    int depth_top;
-    if (k.is_f) {
-        pre = st >= 2;
-        depth_top = 2 * st - 3;
-        if (st == 0) { dir = k.wo; allow_r = false; allow_t = true; }
-        else if (st == 1) { dir = k.wi; allow_r = false; allow_t = true; radiance = false; want_pdf = !smooth; }
-        else { dir = -k.w; allow_r = true; allow_t = false; }
-    } else {
-        pre = st >= 1;
-        depth_top = 2 * st - 1;
-        dir = st == 0 ? k.wo : -k.w;
-        allow_r = allow_t = true;
-    }
-    if (pre) {
-        if (!walk_roulette(k, key, depth_top, 0)) { k.step = -1; return false; }
-        if (k.w.z == 0.0f) { k.step = -1; return false; }
+    bool alive = true;
+    if (walking) {
+        alive = walk_roulette(k, key, is_f ? 2 * st - 3 : 2 * st - 1, 0) && k.w.z != 0.0f;
         k.beta *= transmittance(k.w);
     }
+    const float3 dir = first ? k.wo : (pre_b ? k.wi : -k.w);
     TopSample ts;
-    top_sample(dir, k.alpha, allow_r, allow_t, radiance, want_pdf, u.uc, u.u1, u.u2, ts);
-    if (!ts.ok) { k.step = -1; return false; }
-    if (k.is_f) {
-        if (st == 0) {
-            k.beta = v3(ts.weight);
-            k.w = ts.wi;
-            k.step = 1;
-            return true;                      // no bottom event in the first step of an f walk
+    //            f walk: wos and wis transmit only, the walk reflects only; sample walk: both lobes
+    top_sample(dir, k.alpha, /*allow_r=*/!is_f || walking, /*allow_t=*/!is_f || !walking, /*radiance=*/!pre_b,
+               /*want_pdf=*/pre_b && !smooth, u.uc, u.u1, u.u2, ts);
+    alive = alive && ts.ok;
+    if (pre_b) {
+        // next-event term along wis at every visit of the base (:318-334): everything but the walk's throughput and
+        // the albedo is constant — diffuse f = albedo / pi, |wis.z|, MIS weight against the base's cosine pdf,
+        // Tr(wis), wis.f / wis.pdf
+        float wt = 1.0f;
+        if (!smooth) {
+            const float base_pdf = fabsf(ts.wi.z) * kInvPi;
+            wt = ts.pdf * ts.pdf / (ts.pdf * ts.pdf + base_pdf * base_pdf);
         }
-        if (st == 1) {
-            // next-event term along wis at every visit of the base (:318-334): everything but the walk's
-            // throughput and the albedo is constant — diffuse f = albedo / pi, |wis.z|, MIS weight against the
-            // base's cosine pdf, Tr(wis), wis.f / wis.pdf
-            float wt = 1.0f;
-            if (!smooth) {
-                const float base_pdf = fabsf(ts.wi.z) * kInvPi;
-                wt = ts.pdf * ts.pdf / (ts.pdf * ts.pdf + base_pdf * base_pdf);
-            }
-            k.c_wis = kInvPi * wt * transmittance(ts.wi) * ts.weight;
-        } else {
-            k.beta *= ts.weight;
-            k.w = ts.wi;
-        }
+        k.c_wis = kInvPi * wt * transmittance(ts.wi) * ts.weight;
     } else {
-        if (st == 0) k.beta = v3(ts.weight); else k.beta *= ts.weight;
+        k.beta = first ? v3(ts.weight) : k.beta * ts.weight;
         k.w = ts.wi;
-        if (st == 0 ? ts.reflected : !ts.reflected) {   // left the layers: reflected off the top at once, or transmitted out from below
-            if (k.flipped) k.w = -k.w;
-            k.ok = true;
-            k.step = -1;
-            return false;
-        }
-        if (st == kStepsS - 1) { k.step = -1; return false; }   // depth 9 did not leave: no sample (:513)
     }
+    // the sample walk leaves the layers by reflecting off the top at once or by transmitting out from below;
+    // its depth-9 event is the last chance (:513)
+    const bool exits = alive && !is_f && (first ? ts.reflected : !ts.reflected);
+    const bool last_s = !is_f && st == kStepsS - 1;
+    // no bottom event in the first step of an f walk
+    bool bottom = alive && !exits && !last_s && !(is_f && first);
 
     // ---- bottom ----
-    const int depth_bot = k.is_f ? 2 * st - 2 : 2 * st;
-    if (!walk_roulette(k, key, depth_bot, 1)) { k.step = -1; return false; }
-    if (k.w.z == 0.0f) { k.step = -1; return false; }
-    k.beta *= transmittance(k.w);
-    if (k.is_f) k.f += k.beta * k.albedo * k.c_wis;
-    // cosine sample of the base (LambertDiffuse.h:110-132): weight = albedo exactly
-    const float r = sqrtf(u.d1);
-    float sn, cs;
-    fsincos(2.0f * kPi * u.d2 - kPi, sn, cs);
-    const float3 up = v3(r * cs, r * sn, sqrtf(fmaxf(0.0f, 1.0f - u.d1)));
-    k.beta *= k.albedo;
-    if (!(max3(k.beta) > 0.0f) || up.z == 0.0f) { k.step = -1; return false; }
-    if (k.is_f && !smooth) k.f += k.beta * (transmittance(up) * exit_term(up, k.wi, a2, k.lam_wi));
-    k.w = up;
-    k.step = st + 1;
-    if (k.is_f && st == kStepsF - 1) { k.step = -1; return false; }
-    return true;
+    if (bottom) {
+        bottom = walk_roulette(k, key, is_f ? 2 * st - 2 : 2 * st, 1) && k.w.z != 0.0f;
+        k.beta *= transmittance(k.w);
+        if (bottom && is_f) k.f += k.beta * k.albedo * k.c_wis;
+        // cosine sample of the base (LambertDiffuse.h:110-132): weight = albedo exactly
+        const float r = sqrtf(u.d1);
+        float sn, cs;
+        fsincos(2.0f * kPi * u.d2 - kPi, sn, cs);
+        const float3 up = v3(r * cs, r * sn, sqrtf(fmaxf(0.0f, 1.0f - u.d1)));
+        k.beta *= k.albedo;
+        bottom = bottom && max3(k.beta) > 0.0f && up.z != 0.0f;
+        if (bottom && is_f && !smooth) k.f += k.beta * (transmittance(up) * exit_term(up, k.wi, a2, k.lam_wi));
+        k.w = up;
+    }
+
+    // ---- what happens next ----
+    if (exits) {
+        if (k.flipped) k.w = -k.w;
+        k.ok = true;
+    }
+    const bool f_first_ok = alive && is_f && first;
+    const bool go_on = f_first_ok || (bottom && !(is_f && st == kStepsF - 1));
+    k.step = go_on ? st + 1 : -1;
+    return go_on;
 }
 
 }  // namespace fastlayer

@@ -64,5 +64,10 @@ struct B2ptRenderer {
     double ms_kernel[5] = {0, 0, 0, 0, 0};
     uint64_t launches_kernel_cls[5] = {0, 0, 0, 0, 0};
 
+    // one process per device (multi.cu, b2pt_dist_*): the NCCL communicator this renderer reduces over
+    void* dist_comm = nullptr;   // ncclComm_t
+    int dist_rank = 0, dist_world = 1;
+    b2pt::DeviceBuffer<unsigned long long> d_dist_count;   // [0] this rank's samples, [1] their sum on the root
+
     void set_error(const std::string& m) { last_error = m; }
 };

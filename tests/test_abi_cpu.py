@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), n
     assert set(names) == set(_lib.SIGNATURES), set(names) ^ set(_lib.SIGNATURES)
-    assert lib.b2pt_abi_version() == 3
+    assert lib.b2pt_abi_version() == 4
 
 
 def test_struct_sizes_match_the_header():

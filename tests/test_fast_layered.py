@@ -169,7 +169,7 @@ import sys, numpy as np
 sys.path.insert(0, %r)
 from optixpathtracer_b200 import OptixRenderer, scenes
 sc = scenes.spheres_scene(segments=32, rings=16, metallic=0.0)
-with OptixRenderer(None, sc, bsdf_mode="layered", rng_mode="philox", max_bounces=8) as r:
+with OptixRenderer(None, sc, bsdf_mode="layered", rng_mode="philox", seed=int(sys.argv[2]), max_bounces=8) as r:
     r.Resize((160, 160)); r.SetCamera(sc["camera"]); r.SetLights(sc["lights"])
     a = r.RenderAccumulate(256)
     st = r.Stats()
@@ -181,26 +181,33 @@ print("RAYS", st["radiance_rays"], st["shadow_rays"], st["shadow_rays_traced"])
 @pytest.mark.gpu
 def test_engine_image_equals_the_serial_kernel_image(tmp_path):
     """The same scene rendered by the walk engine and by the serial k_shade<LAYERED> (B2PT_LAYERED_ENGINE=0), both
-    with Philox: two independent estimates of one integral.  Their difference must be noise: the per-pixel
-    difference, normalised by the per-pixel standard error estimated from the two images' local variance, has
-    no bias (mean over the image within a few standard errors of 0)."""
+    with Philox: independent estimates of one integral.  Their difference must be noise — no larger than the
+    difference between two SERIAL renders with different seeds (the noise floor at this sample count), by the
+    same measures: global mean, per-tile means (median and 99th percentile of the relative difference), MSE of
+    the display-referred image.  And the engine's image must not depend on how tasks were handed to lanes."""
     from tests import image_metrics as im
     imgs = {}
-    for tag, env in (("engine", {}), ("serial", {"B2PT_LAYERED_ENGINE": "0"}), ("engine2", {"B2PT_ENGINE_REFILL": "1"})):
+    for tag, env, seed in (("engine", {}, 1), ("engine_refill1", {"B2PT_ENGINE_REFILL": "1"}, 1),
+                           ("serial_a", {"B2PT_LAYERED_ENGINE": "0"}, 2), ("serial_b", {"B2PT_LAYERED_ENGINE": "0"}, 3)):
         e = {k: v for k, v in os.environ.items() if not k.startswith("B2PT_")}
         e.update(env)
         out = tmp_path / f"{tag}.npy"
-        p = subprocess.run([sys.executable, "-c", PROBE % str(ROOT), str(out)], env=e, capture_output=True, text=True, timeout=600)
+        p = subprocess.run([sys.executable, "-c", PROBE % str(ROOT), str(out), str(seed)], env=e, capture_output=True, text=True, timeout=600)
         assert p.returncode == 0, p.stderr[-2000:]
         imgs[tag] = np.load(out).astype(np.float64)
-    assert np.array_equal(imgs["engine"], imgs["engine2"]), "the engine's image depends on how tasks were handed to lanes"
-    a, b = imgs["engine"], imgs["serial"]
-    assert np.isfinite(a).all()
-    # global energy: the two means agree to a fraction of a percent at 256 spp x 25 600 pixels
-    assert abs(a.mean() - b.mean()) <= 0.004 * b.mean(), (a.mean(), b.mean())
-    # per-channel, per-region (8x8 tiles): no region is biased
-    t = lambda x: x.reshape(20, 8, 20, 8, 3).mean((1, 3))
-    ta, tb = t(a), t(b)
-    rel = np.abs(ta - tb) / np.maximum(tb, 1e-3)
-    assert np.median(rel) < 0.02 and np.percentile(rel, 99) < 0.15, (np.median(rel), np.percentile(rel, 99))
-    assert im.mse(np.clip(a, 0, 1), np.clip(b, 0, 1)) < 2e-4
+    assert np.array_equal(imgs["engine"], imgs["engine_refill1"]), "the engine's image depends on how tasks were handed to lanes"
+    assert np.isfinite(imgs["engine"]).all()
+
+    def measures(a, b):
+        t = lambda x: x.reshape(20, 8, 20, 8, 3).mean((1, 3))
+        rel = np.abs(t(a) - t(b)) / np.maximum(0.5 * (t(a) + t(b)), 1e-3)
+        return (abs(a.mean() - b.mean()) / b.mean(), np.median(rel), np.percentile(rel, 99),
+                im.mse(np.clip(a, 0, 1), np.clip(b, 0, 1)))
+
+    floor = measures(imgs["serial_a"], imgs["serial_b"])
+    for other in ("serial_a", "serial_b"):
+        got = measures(imgs["engine"], imgs[other])
+        assert got[0] <= max(3.0 * floor[0], 0.004), ("global mean", got, floor)
+        assert got[1] <= 1.5 * floor[1] + 1e-3, ("median tile difference", got, floor)
+        assert got[2] <= 2.0 * floor[2] + 1e-2, ("99th percentile tile difference", got, floor)
+        assert got[3] <= 1.5 * floor[3] + 1e-7, ("display MSE", got, floor)
