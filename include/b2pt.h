@@ -162,6 +162,19 @@ typedef struct B2ptStats {
      * triangles_tested / warp_slots_tri are the SIMD utilisation of the two loops.          */
     uint64_t warp_slots_node;
     uint64_t warp_slots_tri;
+    /* the walk engine of the layered BSDF (production generator; csrc/shade_layered.cu): device time and
+     * launches of the engine kernel alone (both are also inside device_ms_kernel[3] / launches_kernel[3]),
+     * hits whose f was evaluated (five walk tasks each) and hits that ran a sample walk (one task each)   */
+    double   device_ms_engine;
+    uint64_t launches_engine;
+    uint64_t walk_f_hits;
+    uint64_t walk_s_hits;
+    /* acceleration structure as built: wide nodes the traversal can reach (the compacted array K5/K8 read),
+     * levels of the binary and of the wide tree (the traversal stacks hold 64 and 3 x 64 entries)          */
+    int32_t  n_wide_nodes;
+    int32_t  bvh_depth;
+    int32_t  bvh_wide_depth;
+    int32_t  reserved0;
 } B2ptStats;
 
 typedef struct B2ptRenderer B2ptRenderer;

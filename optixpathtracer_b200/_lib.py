@@ -67,7 +67,11 @@ class B2ptStats(C.Structure):
                 ("exact_tests_shadow", C.c_uint64),
                 ("device_ms_kernel", C.c_double * 5), ("launches_kernel", C.c_uint64 * 5),
                 ("shadow_rays_traced", C.c_uint64), ("warp_slots_node", C.c_uint64),
-                ("warp_slots_tri", C.c_uint64)]
+                ("warp_slots_tri", C.c_uint64),
+                ("device_ms_engine", C.c_double), ("launches_engine", C.c_uint64),
+                ("walk_f_hits", C.c_uint64), ("walk_s_hits", C.c_uint64),
+                ("n_wide_nodes", C.c_int32), ("bvh_depth", C.c_int32), ("bvh_wide_depth", C.c_int32),
+                ("reserved0", C.c_int32)]
 
 
 # name -> (restype, argtypes); exactly the symbols include/b2pt.h declares.

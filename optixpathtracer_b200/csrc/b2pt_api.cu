@@ -324,6 +324,15 @@ int b2pt_get_stats(const B2ptRenderer* rc, B2ptStats* out) {
             out->device_ms_kernel[k] = r->ms_kernel[k];
             out->launches_kernel[k] = r->launches_kernel_cls[k];
         }
+        out->device_ms_kernel[kClsShade] += r->ms_kernel[kClsEngine];   // the engine is a shade kernel
+        out->launches_kernel[kClsShade] += r->launches_kernel_cls[kClsEngine];
+        out->device_ms_engine = r->ms_kernel[kClsEngine];
+        out->launches_engine = r->launches_kernel_cls[kClsEngine];
+        out->n_wide_nodes = r->scene.n_wide_nodes;
+        out->bvh_depth = r->scene.depth;
+        out->bvh_wide_depth = r->scene.wide_depth;
+        out->walk_f_hits = c.walk_f_hits;
+        out->walk_s_hits = c.walk_s_hits;
         out->shadow_rays_traced = out->shadow_rays - c.shadow_culled;
         out->warp_slots_node = c.node_slots;
         out->warp_slots_tri = c.tri_slots;
@@ -344,7 +353,7 @@ int b2pt_reset_stats(B2ptRenderer* r) {
         r->kernel_launches = 0;
         r->hook_radiance_rays = r->hook_shadow_rays = 0;
         r->device_ms_render = 0.0;
-        for (int k = 0; k < 5; k++) { r->ms_kernel[k] = 0.0; r->launches_kernel_cls[k] = 0; }
+        for (int k = 0; k < kClsCount; k++) { r->ms_kernel[k] = 0.0; r->launches_kernel_cls[k] = 0; }
         B2PT_CUDA(cudaStreamSynchronize(r->stream));
     });
 }

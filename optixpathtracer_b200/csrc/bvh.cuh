@@ -50,6 +50,14 @@ struct alignas(16) BvhNode4 {
 static_assert(sizeof(BvhNode4) == 128, "wide node must be 128 bytes");
 constexpr int32_t kEmptyChild = 0x7ffffffe;
 
+// Traversal stacks (per ray): the binary kernels push one entry per level below the root plus a sentinel, the wide
+// kernels at most three per level plus the sentinel.  A Karras tree over 63-bit Morton keys with index tie-breaks
+// can be 63 + log2(n) levels deep (many triangles in one Morton cell, a teapot in a stadium), so the build MEASURES
+// the depth of both trees (K3e) and refuses a scene the stack of its traversal kernel could not hold
+// (B2PT_E_UNSUPPORTED) — the kernels themselves push without a bound check.
+constexpr int kStackSize = 64;
+constexpr int kWideStackSize = 3 * kStackSize;
+
 // The 4-wide node in 64 bytes (what K5/K8 read by default): 4 x LDG.128 per visit instead of 7.  The
 // traversal kernels are bound by L1TEX wavefronts — divergent lanes, one wavefront per lane per load
 // instruction (profiles/r01_k_closest_wide_full_summary.txt: L1TEX 67 % busy, issue 53 %) — so the number

@@ -402,8 +402,7 @@ __device__ __forceinline__ BvhNode4Q quantise4(const Slot4 sl[4]) {
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restrict__ wide, BvhNode4Q* __restrict__ wideq,
-            BvhNode4P* __restrict__ widep, int greedy) {
+k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restrict__ wide, int greedy) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_nodes) return;
     const BvhNode2 nd = nodes[i];
@@ -443,8 +442,6 @@ k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restric
         sl[k].lx = sl[k].hx = sl[k].ly = sl[k].hy = sl[k].lz = sl[k].hz = INFINITY;
         sl[k].child = kEmptyChild;
     }
-    if (wideq) wideq[i] = quantise4(sl);
-    if (widep) widep[i] = pack4(sl);
     BvhNode4 w;
     w.lox = make_float4(sl[0].lx, sl[1].lx, sl[2].lx, sl[3].lx); w.hix = make_float4(sl[0].hx, sl[1].hx, sl[2].hx, sl[3].hx);
     w.loy = make_float4(sl[0].ly, sl[1].ly, sl[2].ly, sl[3].ly); w.hiy = make_float4(sl[0].hy, sl[1].hy, sl[2].hy, sl[3].hy);
@@ -452,6 +449,84 @@ k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restric
 #pragma unroll
     for (int j = 0; j < 4; j++) { w.child[j] = sl[j].child; w.pad[j] = 0; }
     wide[i] = w;
+}
+
+
+// ---- K3e: compaction of the wide nodes ("optixAccelCompact", OptixRenderer.cpp:440) ---------------------------
+// K3d writes one wide node per BINARY node, but a descent from the root crosses one to three binary levels per
+// step, so only a part of them can ever be reached (README scene: 58 k of 143 k).  The reachable ones are
+// numbered breadth-first — the levels every ray walks through end up next to each other at the front of the
+// array, whatever the triangle count — the child indices are rewritten, and only the format the traversal
+// kernels read is kept.  The breadth-first sweep also measures the depth of the tree, which the build checks
+// against the traversal stacks (kStackSize, kWideStackSize) instead of trusting it.
+constexpr int kMaxLevels = 128;   // > 63 + 32 (Morton-63 prefix + index tie-break levels, bvh.cuh)
+
+// one level of the sweep: children of the nodes in `fin` are appended to `fout` (order irrelevant: sorted below)
+template <bool WIDE>
+__global__ void __launch_bounds__(kThreads)
+k_bfs_level(const BvhNode4* __restrict__ wide, const BvhNode2* __restrict__ nodes, const int* __restrict__ fin,
+            int* __restrict__ fout, uint32_t* __restrict__ counts, int L, int* __restrict__ level) {
+    const uint32_t n_in = counts[L];
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n_in; j += gridDim.x * blockDim.x) {
+        const int i = fin[j];
+        int c[4];
+        if (WIDE) {
+            const int4 ch = *reinterpret_cast<const int4*>(wide[i].child);
+            c[0] = ch.x; c[1] = ch.y; c[2] = ch.z; c[3] = ch.w;
+        } else {
+            c[0] = nodes[i].child0; c[1] = nodes[i].child1; c[2] = c[3] = kEmptyChild;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (c[k] >= 0 && c[k] != kEmptyChild) {
+                if (level) level[c[k]] = L + 1;
+                fout[atomicAdd(&counts[L + 1], 1u)] = c[k];
+            }
+    }
+}
+__global__ void k_bfs_init(int* fin, uint32_t* counts, int* level) {
+    fin[0] = 0;
+    counts[0] = 1u;
+    if (level) level[0] = 0;
+}
+// sort key = (level, old index): breadth-first, and inside a level in the order of the Morton-sorted binary nodes
+__global__ void __launch_bounds__(kThreads)
+k_compact_keys(int n_nodes, const int* __restrict__ level, uint64_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    keys[i] = level[i] >= 0 ? (((uint64_t)(uint32_t)level[i] << 32) | (uint32_t)i) : ((uint64_t)0xffull << 32 | (uint32_t)i);
+    vals[i] = (uint32_t)i;
+}
+__global__ void __launch_bounds__(kThreads)
+k_compact_remap(int n_reach, const uint32_t* __restrict__ order, int* __restrict__ remap) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n_reach) remap[order[j]] = j;
+}
+__global__ void __launch_bounds__(kThreads)
+k_compact_emit(int n_reach, const uint32_t* __restrict__ order, const int* __restrict__ remap,
+               const BvhNode4* __restrict__ wide, BvhNode4* __restrict__ out4, BvhNode4Q* __restrict__ outq,
+               BvhNode4P* __restrict__ outp) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_reach) return;
+    const BvhNode4 w = wide[order[j]];
+    Slot4 sl[4];
+    const float lx[4] = {w.lox.x, w.lox.y, w.lox.z, w.lox.w}, hx[4] = {w.hix.x, w.hix.y, w.hix.z, w.hix.w};
+    const float ly[4] = {w.loy.x, w.loy.y, w.loy.z, w.loy.w}, hy[4] = {w.hiy.x, w.hiy.y, w.hiy.z, w.hiy.w};
+    const float lz[4] = {w.loz.x, w.loz.y, w.loz.z, w.loz.w}, hz[4] = {w.hiz.x, w.hiz.y, w.hiz.z, w.hiz.w};
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        sl[k].lx = lx[k]; sl[k].hx = hx[k]; sl[k].ly = ly[k]; sl[k].hy = hy[k]; sl[k].lz = lz[k]; sl[k].hz = hz[k];
+        const int c = w.child[k];
+        sl[k].child = (c >= 0 && c != kEmptyChild) ? remap[c] : c;
+    }
+    if (outq) outq[j] = quantise4(sl);
+    if (outp) outp[j] = pack4(sl);
+    if (out4) {
+        BvhNode4 o = w;
+#pragma unroll
+        for (int k = 0; k < 4; k++) o.child[k] = sl[k].child;
+        out4[j] = o;
+    }
 }
 
 // single-triangle scene: one node, second child never hit
@@ -518,6 +593,7 @@ DeviceScene SceneBuffers::view() const {
     s.materials = materials.get();
     s.textures = textures.get();
     s.n_nodes = n_nodes;
+    s.n_wide_nodes = n_wide_nodes;
     s.n_tris = n_tris;
     s.n_meshes = n_meshes;
     s.n_textures = n_textures;
@@ -642,9 +718,11 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
     create_textures(desc, out, stream);
     out.n_nodes = n == 0 ? 0 : (n == 1 ? 1 : n - 1);
     out.nodes.alloc((size_t)out.n_nodes);
-    out.nodes4.alloc((size_t)out.n_nodes);
-    out.nodes4q.alloc((size_t)out.n_nodes);
-    out.nodes4p.alloc((size_t)out.n_nodes);
+    out.nodes4.release();
+    out.nodes4q.release();
+    out.nodes4p.release();
+    out.n_wide_nodes = 0;
+    out.depth = out.wide_depth = 0;
     out.tris.alloc((size_t)n);
     out.nrms.alloc((size_t)n);
     out.uvs.alloc(any_uv ? (size_t)n : 0);
@@ -732,13 +810,88 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
     } else {
         k_emit_single<<<1, 1, 0, stream>>>(d_wv.get(), pad, out.nodes.get());
     }
-    if (out.n_nodes > 0)
-        k_collapse4<<<blocks_for(out.n_nodes), kThreads, 0, stream>>>(out.n_nodes, out.nodes.get(), out.nodes4.get(), out.nodes4q.get(), out.nodes4p.get(), collapse_greedy());
     k_emit_tris<<<blocks_for(n), kThreads, 0, stream>>>(n, d_wv.get(), d_nrm.get(), order, d_tri_mesh.get(),
                                                          d_infos.get(), d_idx.get(), d_uv.get(),
                                                          out.tris.get(), out.nrms.get(), out.uvs.get());
     B2PT_CUDA(cudaGetLastError());
     B2PT_CUDA(cudaMemcpyAsync(out.tri_order.get(), order, (size_t)n * 4, cudaMemcpyDeviceToDevice, stream));
+    // (the compaction below reuses the sort buffers `order` lives in: the triangles are emitted first)
+    if (out.n_nodes > 0) {
+        // K3d into a temporary, one wide node per binary node; K3e keeps the reachable ones, breadth-first
+        const int nn = out.n_nodes;
+        DeviceBuffer<BvhNode4> d_wide;
+        DeviceBuffer<int> d_level, d_front[2], d_remap;
+        DeviceBuffer<uint32_t> d_counts;
+        d_wide.alloc((size_t)nn);
+        d_level.alloc((size_t)nn);
+        d_front[0].alloc((size_t)nn); d_front[1].alloc((size_t)nn);
+        d_remap.alloc((size_t)nn);
+        d_counts.alloc(2 * (kMaxLevels + 1));
+        k_collapse4<<<blocks_for(nn), kThreads, 0, stream>>>(nn, out.nodes.get(), d_wide.get(), collapse_greedy());
+        B2PT_CUDA(cudaMemsetAsync(d_level.get(), 0xff, (size_t)nn * 4, stream));
+        d_counts.zero(stream);
+        uint32_t* cw = d_counts.get();                     // per-level node counts of the wide tree ...
+        uint32_t* cb = d_counts.get() + kMaxLevels + 1;    // ... and of the binary tree (depth only)
+        const int sweep_grid = 148 * 2;
+        k_bfs_init<<<1, 1, 0, stream>>>(d_front[0].get(), cw, d_level.get());
+        for (int L = 0; L < kMaxLevels; L++)
+            k_bfs_level<true><<<sweep_grid, kThreads, 0, stream>>>(d_wide.get(), nullptr, d_front[L & 1].get(), d_front[(L + 1) & 1].get(),
+                                                                    cw, L, d_level.get());
+        std::vector<uint32_t> h_counts(2 * (kMaxLevels + 1));
+        if (n > 1) {
+            k_bfs_init<<<1, 1, 0, stream>>>(d_front[0].get(), cb, nullptr);
+            for (int L = 0; L < kMaxLevels; L++)
+                k_bfs_level<false><<<sweep_grid, kThreads, 0, stream>>>(nullptr, out.nodes.get(), d_front[L & 1].get(),
+                                                                         d_front[(L + 1) & 1].get(), cb, L, nullptr);
+        }
+        d_counts.download(h_counts.data(), h_counts.size(), stream);
+        B2PT_CUDA(cudaStreamSynchronize(stream));
+        int n_reach = 0;
+        for (int L = 0; L <= kMaxLevels; L++) {
+            if (h_counts[L]) out.wide_depth = L + 1;
+            n_reach += (int)h_counts[L];
+            if (h_counts[kMaxLevels + 1 + L]) out.depth = L + 1;
+        }
+        if (n == 1) out.depth = 1;
+        B2PT_REQUIRE(h_counts[kMaxLevels] == 0 && h_counts[2 * kMaxLevels + 1] == 0, B2PT_E_UNSUPPORTED,
+                     "acceleration structure deeper than 128 levels");
+        out.n_wide_nodes = n_reach;
+        // order = reachable nodes by (level, old index): five 8-bit passes cover level (8 bits) + index (32 bits)
+        k_compact_keys<<<blocks_for(nn), kThreads, 0, stream>>>(nn, d_level.get(), d_keys[0].get(), d_vals[0].get());
+        const int nt2 = (nn + kRsTile - 1) / kRsTile;
+        int cur2 = 0;
+        for (int pass = 0; pass < 5; pass++) {
+            const int shift = pass * 8;
+            k_rs_hist<<<nt2, kRsWarps * 32, 0, stream>>>(nn, d_keys[cur2].get(), shift, nt2, d_hist.get());
+            k_rs_scan<<<1, 1024, 0, stream>>>(256 * nt2, d_hist.get());
+            k_rs_scatter<<<nt2, kRsWarps * 32, 0, stream>>>(nn, d_keys[cur2].get(), d_vals[cur2].get(), d_keys[cur2 ^ 1].get(),
+                                                            d_vals[cur2 ^ 1].get(), shift, nt2, d_hist.get());
+            cur2 ^= 1;
+        }
+        const uint32_t* worder = d_vals[cur2].get();
+        k_compact_remap<<<blocks_for(n_reach), kThreads, 0, stream>>>(n_reach, worder, d_remap.get());
+        const int fmt = trace_wide_formats();   // bit 0: BvhNode4, bit 1: BvhNode4Q, bit 2: BvhNode4P
+        if (fmt & 1) out.nodes4.alloc((size_t)n_reach);
+        if (fmt & 2) out.nodes4q.alloc((size_t)n_reach);
+        if (fmt & 4) out.nodes4p.alloc((size_t)n_reach);
+        k_compact_emit<<<blocks_for(n_reach), kThreads, 0, stream>>>(n_reach, worder, d_remap.get(), d_wide.get(),
+                                                                      out.nodes4.get(), out.nodes4q.get(), out.nodes4p.get());
+        B2PT_CUDA(cudaGetLastError());
+        B2PT_CUDA(cudaStreamSynchronize(stream));   // the temporaries above die with this scope
+    }
+    // the stack the scene's traversal kernel has must hold the deepest descent (bvh.cuh)
+    {
+        char msg[160];
+        if (trace_uses_wide(any_alpha)) {
+            snprintf(msg, sizeof msg, "acceleration structure too deep for the traversal stack: %d wide levels, at most %d",
+                     out.wide_depth, (kWideStackSize - 1) / 3);
+            B2PT_REQUIRE(3 * out.wide_depth + 1 <= kWideStackSize, B2PT_E_UNSUPPORTED, msg);
+        } else {
+            snprintf(msg, sizeof msg, "acceleration structure too deep for the traversal stack: %d levels, at most %d "
+                     "(scenes with an alpha-tested texture use the binary-node kernels)", out.depth, kStackSize - 1);
+            B2PT_REQUIRE(out.depth + 1 <= kStackSize, B2PT_E_UNSUPPORTED, msg);
+        }
+    }
     B2PT_CUDA(cudaEventRecord(ev1, stream));
     B2PT_CUDA(cudaStreamSynchronize(stream));
     B2PT_CUDA(cudaEventElapsedTime(&out.build_ms, ev0, ev1));

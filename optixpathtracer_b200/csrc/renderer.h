@@ -61,8 +61,8 @@ struct B2ptRenderer {
     std::vector<cudaEvent_t> timing_events;   // pool, reused by every render call
     std::vector<int> timing_tags;             // class of the kernel that ended at event i+1
     size_t timing_used = 0;
-    double ms_kernel[5] = {0, 0, 0, 0, 0};
-    uint64_t launches_kernel_cls[5] = {0, 0, 0, 0, 0};
+    double ms_kernel[b2pt::kClsCount] = {0, 0, 0, 0, 0, 0};
+    uint64_t launches_kernel_cls[b2pt::kClsCount] = {0, 0, 0, 0, 0, 0};
 
     // one process per device (multi.cu, b2pt_dist_*): the NCCL communicator this renderer reduces over
     void* dist_comm = nullptr;   // ncclComm_t

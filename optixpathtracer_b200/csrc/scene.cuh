@@ -51,7 +51,8 @@ struct DeviceScene {
     const UvRecord* uvs;            // nullptr when no mesh has texcoords
     const MaterialRecord* materials;
     const cudaTextureObject_t* textures;
-    int32_t n_nodes;
+    int32_t n_nodes;                // binary nodes
+    int32_t n_wide_nodes;           // wide nodes the traversal can reach (the compacted arrays above)
     int32_t n_tris;
     int32_t n_meshes;
     int32_t n_textures;
@@ -73,6 +74,8 @@ struct SceneBuffers {
     std::vector<cudaArray_t> texture_arrays;
     std::vector<cudaTextureObject_t> texture_objects;
     int32_t n_tris = 0, n_nodes = 0, n_meshes = 0, n_textures = 0, any_alpha_texture = 0;
+    int32_t n_wide_nodes = 0;           // reachable wide nodes, numbered breadth-first (K3e)
+    int32_t depth = 0, wide_depth = 0;  // levels of the binary / wide tree, measured by the build
     float build_ms = 0.0f;
     float3 bounds_lo = {0, 0, 0}, bounds_hi = {0, 0, 0};
 
@@ -80,6 +83,12 @@ struct SceneBuffers {
     int64_t device_bytes() const;
     void free_textures();
 };
+
+// what the selected traversal kernels need from the build (trace_kernels.cu): wide-node formats they read
+// (bit 0 BvhNode4, bit 1 BvhNode4Q, bit 2 BvhNode4P — the build keeps only those), and whether a scene goes
+// through the wide kernels or the binary ones (decides which stack bound the build checks)
+int trace_wide_formats();
+bool trace_uses_wide(int any_alpha_texture);
 
 // Upload + flatten + LBVH build (K1-K3) on `stream`.  Throws b2pt::Error.
 void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stream);

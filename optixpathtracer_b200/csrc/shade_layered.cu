@@ -177,8 +177,13 @@ k_layered_engine(LayeredScratch ls, const uint32_t* __restrict__ lq, const uint3
 // ---- K7d-f -------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kWaveThreads)
 k_layered_finish(WaveParams wp, PathState st, PathState nx, SurfaceState sf, LayeredScratch ls,
-                 const uint32_t* __restrict__ lq, WaveCounts wc, uint32_t bounce, float* __restrict__ wave_out) {
+                 const uint32_t* __restrict__ lq, WaveCounts wc, const uint32_t* __restrict__ lcounts, uint32_t bounce,
+                 float* __restrict__ wave_out, TraceCounters* __restrict__ counters) {
     const uint32_t n = wc.queued[4 * bounce + kBsdfLayered];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(&counters->walk_f_hits, (unsigned long long)lcounts[0]);
+        atomicAdd(&counters->walk_s_hits, (unsigned long long)n);
+    }
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t iters = (n + stride - 1) / stride;
     for (uint32_t it = 0; it < iters; it++) {
@@ -282,19 +287,24 @@ bool layered_engine_enabled() {
 
 size_t layered_scratch_bytes_per_path() { return (size_t)kLayeredScratchWords * 4; }
 
-// enqueue K7d-p, K7d-e, K7d-f for bounce b; returns the kernels launched
-int launch_layered_engine(B2ptRenderer* r, const WaveParams& wp, const PathState& cur, const PathState& nxt,
-                          const WaveCounts& wc, uint32_t* lcounts, uint32_t bounce) {
+// K7d-p, K7d-e, K7d-f of bounce `bounce`, one call each so that the scheduler can time them apart
+void launch_layered_prep(B2ptRenderer* r, const WaveParams& wp, const PathState& cur, const WaveCounts& wc,
+                         uint32_t* lcounts, uint32_t bounce) {
+    const LayeredScratch ls = scratch_view(r, wp.capacity);
+    const uint32_t* lq = r->d_queues.get() + (size_t)kBsdfLayered * wp.capacity;
+    k_layered_prep<<<r->sm_count * 8, kWaveThreads, 0, r->stream>>>(wp, cur, r->surf, ls, lq, wc.queued, lcounts, bounce);
+}
+
+void launch_layered_walks(B2ptRenderer* r, const WaveParams& wp, const WaveCounts& wc, uint32_t* lcounts, uint32_t bounce) {
     cudaStream_t s = r->stream;
     const LayeredScratch ls = scratch_view(r, wp.capacity);
     const uint32_t* lq = r->d_queues.get() + (size_t)kBsdfLayered * wp.capacity;
-    const int grid = r->sm_count * 8;
-    k_layered_prep<<<grid, kWaveThreads, 0, s>>>(wp, cur, r->surf, ls, lq, wc.queued, lcounts, bounce);
-    // A/B: B2PT_ENGINE_REFILL = idle lanes that trigger a fetch (1 | 4 | 8 | 16 | 32), B2PT_ENGINE_OCC = blocks per SM
-    static const int refill = [] { const char* e = getenv("B2PT_ENGINE_REFILL"); return e ? atoi(e) : 32; }();
+    // A/B (profiles/r02_ab_layered_engine_c4.txt): B2PT_ENGINE_REFILL = idle lanes that trigger a fetch
+    // (1 | 4 | 8 | 16 | 32; 16: c4 573 Msamples/s against 507 at 1 and 542 at 32 — a fetch runs with few lanes, a
+    // whole idle half-warp does not cost more than that), B2PT_ENGINE_OCC = blocks per SM (4 | 6 | 8)
+    static const int refill = [] { const char* e = getenv("B2PT_ENGINE_REFILL"); return e ? atoi(e) : 16; }();
     static const int occ = [] { const char* e = getenv("B2PT_ENGINE_OCC"); return e ? atoi(e) : 6; }();
-#define B2PT_ENGINE(R, O) \
-    k_layered_engine<R, O><<<r->sm_count * O, kWaveThreads, 0, s>>>(ls, lq, wc.queued, lcounts, bounce)
+#define B2PT_ENGINE(R, O) k_layered_engine<R, O><<<r->sm_count * O, kWaveThreads, 0, s>>>(ls, lq, wc.queued, lcounts, bounce)
     if (occ >= 8) {
         if (refill >= 32) B2PT_ENGINE(32, 8); else if (refill >= 16) B2PT_ENGINE(16, 8); else if (refill >= 8) B2PT_ENGINE(8, 8);
         else if (refill >= 4) B2PT_ENGINE(4, 8); else B2PT_ENGINE(1, 8);
@@ -306,8 +316,14 @@ int launch_layered_engine(B2ptRenderer* r, const WaveParams& wp, const PathState
         else if (refill >= 4) B2PT_ENGINE(4, 4); else B2PT_ENGINE(1, 4);
     }
 #undef B2PT_ENGINE
-    k_layered_finish<<<grid, kWaveThreads, 0, s>>>(wp, cur, nxt, r->surf, ls, lq, wc, bounce, r->d_wave_out.get());
-    return 3;
+}
+
+void launch_layered_finish(B2ptRenderer* r, const WaveParams& wp, const PathState& cur, const PathState& nxt,
+                           const WaveCounts& wc, const uint32_t* lcounts, uint32_t bounce) {
+    const LayeredScratch ls = scratch_view(r, wp.capacity);
+    const uint32_t* lq = r->d_queues.get() + (size_t)kBsdfLayered * wp.capacity;
+    k_layered_finish<<<r->sm_count * 8, kWaveThreads, 0, r->stream>>>(wp, cur, nxt, r->surf, ls, lq, wc, lcounts, bounce,
+                                                                       r->d_wave_out.get(), r->d_counters.get());
 }
 
 void launch_fast_layered_rows_f(int64_t n, const float* albedo, const float* roughness, const float* wo, const float* wi,

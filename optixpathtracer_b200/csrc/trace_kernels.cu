@@ -261,6 +261,13 @@ bool use_persistent() {
 
 int trace_grid_blocks_per_sm() { return occ_blocks() > 0 ? occ_blocks() : 8; }
 
+int trace_wide_formats() {
+    if (!(use_persistent() && use_wide())) return 0;
+    if (use_triq()) return 1;
+    return node_step() == 2 ? 2 : node_step() == 6 ? 4 : 1;
+}
+bool trace_uses_wide(int any_alpha_texture) { return use_persistent() && use_wide() && any_alpha_texture == 0; }
+
 int trace_node_bytes(const DeviceScene& sc) {
     if (use_persistent() && use_wide() && sc.any_alpha_texture == 0)
         return use_triq() ? (int)sizeof(BvhNode4) : node_step() == 2 ? (int)sizeof(BvhNode4Q) : node_step() == 6 ? (int)sizeof(BvhNode4P) : (int)sizeof(BvhNode4);

@@ -11,9 +11,8 @@
 
 namespace b2pt {
 
-// a descent crosses at least one binary level (the greedy collapse, K3d, may open only one side) and
-// pushes at most three entries; the binary tree is at most kStackSize levels deep
-constexpr int kWideStackSize = 3 * kStackSize;
+// kWideStackSize (bvh.cuh): a visit pushes at most three entries; the build refuses trees whose measured wide
+// depth would overflow it
 
 // slab test of slot k of a wide node (same arithmetic as slab(), traverse.cuh)
 #define B2PT_SLAB4(k, comp)                                                                                   \

@@ -147,7 +147,7 @@ B2PT_HD bool slab(const RaySetup& r, float lox, float hix, float loy, float hiy,
     return tn <= tf * 1.000001f;
 }
 
-constexpr int kStackSize = 64;
+// kStackSize / kWideStackSize: bvh.cuh (the build checks the measured depth of the tree against them)
 constexpr int kStackSentinel = 0x7fffffff;
 
 

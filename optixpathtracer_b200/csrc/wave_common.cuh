@@ -46,9 +46,12 @@ constexpr int kCountsWords = 1301 + 400;
 // B2PT_LAYERED_ENGINE=0 sends the Philox mode through the serial k_shade<LAYERED> too (A/B, tests)
 bool layered_engine_enabled();
 size_t layered_scratch_bytes_per_path();
-// enqueue K7d-p/e/f of bounce `bounce` on r->stream; lcounts = 4 zeroed words; returns the kernels launched
-int launch_layered_engine(B2ptRenderer* r, const WaveParams& wp, const PathState& cur, const PathState& nxt,
-                          const WaveCounts& wc, uint32_t* lcounts, uint32_t bounce);
+// K7d-p / K7d-e / K7d-f of bounce `bounce` on r->stream; lcounts = 4 zeroed words (f-list length, task cursor)
+void launch_layered_prep(B2ptRenderer* r, const WaveParams& wp, const PathState& cur, const WaveCounts& wc,
+                         uint32_t* lcounts, uint32_t bounce);
+void launch_layered_walks(B2ptRenderer* r, const WaveParams& wp, const WaveCounts& wc, uint32_t* lcounts, uint32_t bounce);
+void launch_layered_finish(B2ptRenderer* r, const WaveParams& wp, const PathState& cur, const PathState& nxt,
+                           const WaveCounts& wc, const uint32_t* lcounts, uint32_t bounce);
 // parity-hook rows of the engine's per-lane logic (device pointers, default stream)
 void launch_fast_layered_rows_f(int64_t n, const float* albedo, const float* roughness, const float* wo, const float* wi,
                                 const uint32_t* seed, float* f_out);

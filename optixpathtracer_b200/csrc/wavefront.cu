@@ -405,9 +405,13 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
         if (kinds[1]) { k_shade<kBsdfDiffuse, Rng, 8><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 1 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
         if (kinds[2]) { k_shade<kBsdfDielectric, Rng, 8><<<g3, kThreads, 0, s>>>(wp, cur, nxt, r->surf, q + 2 * cap, wc, (uint32_t)b, r->d_wave_out.get()); count(); mark(kClsShade); }
         if (kinds[3] && engine) {
-            count(launch_layered_engine(r, wp, cur, nxt, wc, r->d_counts.get() + kCountsLayered + 4 * b, (uint32_t)b));
-            r->launches_kernel_cls[kClsShade] += 2;
-            mark(kClsShade);
+            uint32_t* lcounts = r->d_counts.get() + kCountsLayered + 4 * b;
+            launch_layered_prep(r, wp, cur, wc, lcounts, (uint32_t)b);
+            count(); mark(kClsShade);
+            launch_layered_walks(r, wp, wc, lcounts, (uint32_t)b);
+            count(); mark(kClsEngine);
+            launch_layered_finish(r, wp, cur, nxt, wc, lcounts, (uint32_t)b);
+            count(); mark(kClsShade);
         } else if (kinds[3]) {
             const uint32_t* q3 = q;
             if (wp.n_lights > 0) {   // K7p: visible hits first in the layered queue

@@ -58,8 +58,10 @@ struct TraceCounters {
     unsigned long long nodes_any, tris_any, exact_any;
     unsigned long long node_slots, tri_slots;   // K5 stats build: lane slots of the node / triangle loops
     unsigned long long shadow_culled;   // shadow rays K6 did not emit because f(wo, wl) is exactly zero
+    unsigned long long walk_f_hits, walk_s_hits;   // layered walk engine: hits with f walks (5 tasks each) / sample walks
 };
-enum KernelClass : int { kClsClosest = 0, kClsAny = 1, kClsSurface = 2, kClsShade = 3, kClsOther = 4, kClsCount = 5 };
+// kClsEngine: the walk-engine kernel of the layered BSDF (K7d-e) on its own; reported inside the shade class too
+enum KernelClass : int { kClsClosest = 0, kClsAny = 1, kClsSurface = 2, kClsShade = 3, kClsOther = 4, kClsEngine = 5, kClsCount = 6 };
 
 // ---- launchers (wavefront.cu / trace_kernels.cu) ---------------------------
 struct LaunchCfg {
@@ -73,6 +75,7 @@ struct LaunchCfg {
 int trace_grid_blocks_per_sm();
 // bytes of the node record K5/K8 read for this scene (64: binary nodes, 128: 4-wide nodes)
 int trace_node_bytes(const DeviceScene& sc);
+
 
 // K5: closest hit for rays [0, *n_active) of `st`; n_active lives on the device.
 void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState& st,

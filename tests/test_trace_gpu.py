@@ -43,7 +43,7 @@ def test_bvh_structure():
         st = r.Stats()
         nt = st["n_triangles"]
         assert nt == sum(len(m["indices"]) for m in sc["meshes"])
-        assert st["n_nodes"] == nt - 1 and st["node_bytes"] in (64, 96, 128) and st["triangle_bytes"] == 48   # 128: 4-wide nodes (default)
+        assert st["n_nodes"] == nt - 1 and st["node_bytes"] in (64, 96, 128) and st["triangle_bytes"] == 48   # 96: the packed 4-wide nodes (default)
         nodes, order = r.DownloadBvh()
         assert sorted(order.tolist()) == list(range(nt))          # a permutation
         child = nodes.view(np.int32)[:, 12:14]
@@ -173,3 +173,108 @@ def test_stats_counters():
         assert st["radiance_rays"] == len(o)
         assert st["nodes_visited"] > len(o) and st["triangles_tested"] > 0
         assert st["exact_tests"] <= st["triangles_tested"]
+
+
+# ---- deep and degenerate trees: the build measures the depth and checks it against the traversal stacks ------------
+def _depth_checked(r, n_tris):
+    st = r.Stats()
+    assert 1 <= st["bvh_wide_depth"] <= st["bvh_depth"] <= 127
+    assert 3 * st["bvh_wide_depth"] + 1 <= 192, "wide traversal stack (kWideStackSize)"
+    assert 1 <= st["n_wide_nodes"] <= max(st["n_nodes"], 1)
+    return st
+
+
+def test_many_coincident_triangles(oracle):
+    """10^5 triangles with ONE centroid cell (exact duplicates and near-duplicates): the Karras build splits them on
+    the index bits — log2(n) extra levels under the deepest Morton prefix.  Exact ties: the lowest primitive id wins."""
+    rng = np.random.default_rng(5)
+    base = np.array([[0.0, 0.0, 0.0], [1e-3, 0.0, 0.0], [0.0, 1e-3, 0.0]], f32)
+    n = 100_000
+    soup = np.tile(base, (n, 1, 1)).astype(f32)
+    soup[n // 2:] += rng.normal(scale=1e-9, size=(n - n // 2, 3, 3)).astype(f32)      # near-duplicates
+    far = rng.uniform(-1, 1, (64, 3, 3)).astype(f32)                                  # a few ordinary triangles around
+    soup = np.concatenate([soup, far])
+    o = np.concatenate([rng.uniform(0, 1e-3, (256, 3)) * [1, 1, 0] + [0, 0, 1.0], rng.uniform(-1, 1, (256, 3))]).astype(f32)
+    d = np.concatenate([np.tile([0, 0, -1.0], (256, 1)), rng.normal(size=(256, 3))])
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(f32)
+    with _renderer(_soup_scene(soup)) as r:
+        st = _depth_checked(r, len(soup))
+        assert st["bvh_depth"] >= 17                  # log2(10^5) levels of index tie-breaks
+        prim, _, _ = _compare(r, oracle, soup, o, d)
+        assert (prim[:256] >= 0).sum() > 50
+        tm = np.full(len(o), 50.0, f32)
+        assert np.array_equal(r.TraceAny(o, d, tm), oracle.any(soup, o, d, tm))
+
+
+def test_teapot_in_a_stadium(oracle):
+    """A 10^-6-scale tessellated sphere inside a unit room: all of its triangles share the last Morton cells, the
+    room's triangles sit 20 octaves above."""
+    pos, _, _, idx = scenes.uv_sphere(32, 16)
+    tiny = (pos[idx].astype(np.float64) * 1e-6 + [0.3, 0.3, 0.3]).astype(f32)
+    room = []
+    for axis in range(3):
+        for side in (0.0, 1.0):
+            q = np.zeros((4, 3))
+            a, b = [k for k in range(3) if k != axis]
+            q[:, axis] = side
+            q[:, a] = [0, 1, 1, 0]
+            q[:, b] = [0, 0, 1, 1]
+            room += [q[[0, 1, 2]], q[[0, 2, 3]]]
+    soup = np.concatenate([tiny, np.array(room, f32)]).astype(f32)
+    rng = np.random.default_rng(9)
+    o1 = rng.uniform(0.05, 0.95, (512, 3))
+    tgt = tiny.reshape(-1, 3)[rng.integers(0, tiny.shape[0] * 3, 512)].astype(np.float64)
+    d1 = tgt + rng.normal(scale=3e-7, size=tgt.shape) - o1
+    o2, d2 = random_rays(rng, 512, [0.05] * 3, [0.95] * 3)
+    o = np.concatenate([o1, o2]).astype(f32)
+    d = np.concatenate([d1 / np.linalg.norm(d1, axis=1, keepdims=True), d2]).astype(f32)
+    with _renderer(_soup_scene(soup)) as r:
+        _depth_checked(r, len(soup))
+        prim, _, _ = _compare(r, oracle, soup, o, d)
+        assert (prim[:512] < len(tiny)).sum() > 100      # the rays aimed at the tiny sphere do find it
+
+
+def test_sliver_chain(oracle):
+    """A geometric chain of slivers: centroids at 2^-k, every Morton level splits one triangle off."""
+    t = []
+    for k in range(1, 40):
+        x = 2.0 ** -k
+        t.append([[x, 0.0, 0.0], [x * 1.5, 1e-4 * x, 0.0], [x, 0.0, 1.0]])       # long thin triangles
+        t.append([[0.0, x, 0.0], [1e-4 * x, x * 1.5, 0.0], [0.0, x, 1.0]])
+    soup = np.array(t, f32)
+    rng = np.random.default_rng(2)
+    o, d = random_rays(rng, 2000, [-0.2, -0.2, -0.2], [1.2, 1.2, 1.2])
+    tgt = soup.reshape(-1, 3)[rng.integers(0, soup.shape[0] * 3, 1000)]
+    o2 = (tgt + rng.normal(scale=0.3, size=tgt.shape)).astype(f32)
+    d2 = tgt - o2
+    d2 = (d2 / np.linalg.norm(d2, axis=1, keepdims=True)).astype(f32)
+    o, d = np.concatenate([o, o2]), np.concatenate([d, d2])
+    with _renderer(_soup_scene(soup)) as r:
+        _depth_checked(r, len(soup))
+        _compare(r, oracle, soup, o, d)
+
+
+def test_too_deep_for_the_binary_kernels_is_refused_not_overrun():
+    """Scenes with an alpha-tested texture traverse the binary tree with a 64-entry stack.  A sliver chain down the
+    Morton levels with 2^10 coincident triangles at its end is deeper than that: b2pt_create must say so
+    (B2PT_E_UNSUPPORTED) — or build a tree that fits; it must never build one that does not."""
+    from optixpathtracer_b200._lib import B2ptError
+    t = []
+    for k in range(1, 22):
+        x = 2.0 ** -k
+        for axis in range(3):
+            p = np.zeros(3)
+            p[axis] = x
+            t.append([p, p + [1e-9, 0, 0], p + [0, 1e-9, 0]])
+    t += [[[0, 0, 0], [1e-9, 0, 0], [0, 1e-9, 0]]] * 1024
+    soup = np.array(t, f32)
+    sc = _soup_scene(soup)
+    sc["meshes"][0]["texcoords"] = np.zeros((len(soup) * 3, 2), f32)
+    sc["meshes"][0]["tex_albedo"] = 0
+    sc["textures"] = [np.full((2, 2, 4), 255, np.uint8)]
+    try:
+        with _renderer(sc) as r:
+            st = r.Stats()
+            assert st["bvh_depth"] + 1 <= 64
+    except B2ptError as e:
+        assert e.code == -5 and "too deep" in str(e)
