@@ -5,12 +5,15 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 Metric (BASELINE.json): Msamples/s — complete camera paths per second, whole job
-over all N GPUs.  Workload at N=1: BASELINE.json configs[1] (README "Conductor"
-scene, 1024x1024, depth 16, 256 spp); a STEP is one pass of the hot path over
-one batch = `spp_per_step` samples of every pixel (default 64, so 4 steps are
-the whole 256-spp config; one step is ONE wave of 2^26 paths, 16 GB of wave state).  Multi-GPU = weak scaling: every rank renders its
-own spp_per_step samples per step (disjoint absolute sample indices, replicated
-scene/BVH) and the fp32 sums are combined with one NCCL reduce per step.
+over all N GPUs.  Workload at N=1: the largest single-GPU configuration of
+BASELINE.json, configs[3] (README "Layered" scene, 1920x1080, depth 8, 1024 spp;
+--config c1|c2|c3|c5 select the others); a STEP is one pass of the hot path over
+one batch = `spp_per_step` samples of every pixel (default 64: one step is ONE
+wave of 2^27 path slots).  Multi-GPU: one process per GPU (torchrun); every rank
+renders disjoint absolute sample indices with a replicated scene/BVH and the fp32
+sums are combined by ONE ncclReduce per step issued by the library itself
+(b2pt_dist_render_accumulate).  --scaling weak (default): spp_per_step per GPU;
+--scaling strong: the step's spp_per_step are split over the GPUs.
 
 One JSON line is printed by rank 0; see DESIGN.md "Measurement" for every key.
 """
@@ -265,13 +268,6 @@ def algorithmic_bytes_per_ray(scene, w, h, depth, mode, spp=1):
             "simd_tri_loop": st["triangles_tested"] / max(st["warp_slots_tri"], 1)}
 
 
-class DevicePtr:
-    """Wraps a raw device pointer for torch.as_tensor (CUDA array interface)."""
-
-    def __init__(self, ptr, n):
-        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 3}
-
-
 def run_b2pt(args, cfg):
     import torch
     import torch.distributed as dist
@@ -296,32 +292,39 @@ def run_b2pt(args, cfg):
                       wave_paths_log2=args.wave_log2)
     r.Resize((w, h)); r.SetCamera(scene["camera"]); r.SetLights(scene["lights"])
     build_ms = r.Stats()["device_ms_build"]
-    ptr, _ = r.AccumulationDevice()
-    acc = torch.as_tensor(DevicePtr(ptr, n_px * 3), device=f"cuda:{local}")
-    total = torch.zeros_like(acc)
+    if world > 1:
+        # torch.distributed is the plumbing (rendezvous, barrier, max over ranks); the reduce of the image is the
+        # library's own ncclReduce on its own stream (b2pt_dist_*): rank 0's 128-byte NCCL id goes to every rank
+        uid = torch.zeros(128, dtype=torch.uint8, device=f"cuda:{local}")
+        if rank == 0:
+            uid.copy_(torch.from_numpy(OptixRenderer.DistUniqueId()))
+        dist.broadcast(uid, src=0)
+        r.DistInit(uid.cpu().numpy(), rank, world)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def step(k, frame_base):
-        # rank g renders absolute samples [base + g*spp, base + (g+1)*spp): disjoint Philox streams
+    def first_sample(k, base=0):
+        # rank g renders absolute samples [base + (k N + g) spp, +spp): disjoint Philox streams
+        return base + (k * n_gpus + rank) * spp
+
+    def step(k, base, out=None):
         r.ClearAccumulation()
-        r.SetFrameId(frame_base + (k * n_gpus + rank) * spp)
-        r.RenderAccumulate(spp, download=False)
+        r.SetFrameId(first_sample(k, base))
         if world > 1:
-            dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)     # one NCCL reduce of W*H*3 fp32 sums
-        if rank == 0:
-            total.add_(acc)
-        torch.cuda.current_stream().synchronize()
+            r.DistRenderAccumulate(spp, out)       # render + ONE ncclReduce + the root's 1/spp epilogue (+ D2H if out)
+        elif out is not None:
+            r.RenderAccumulate(spp, out=out)       # b2pt_render_accumulate: D2H inside the call
+        else:
+            r.RenderAccumulate(spp, download=False)
 
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     for k in range(args.warmup):
         step(k, 1_000_000)
-    total.zero_()
     r.ResetStats()
     r.SetKernelTiming(False)       # `value` is timed without the per-kernel events; shares come from a separate pass below
     barrier()
@@ -332,7 +335,7 @@ def run_b2pt(args, cfg):
     step_ms = []
     for k in range(args.steps):
         ts = time.perf_counter()
-        step(k, 0)             # ends with a stream synchronize
+        step(k, 0)                 # synchronous on return (the library synchronises its stream)
         step_ms.append((time.perf_counter() - ts) * 1e3)
     e1.record()
     barrier()
@@ -348,7 +351,6 @@ def run_b2pt(args, cfg):
     dev_ms, render_ms, wall_ms = [float(x) for x in t.tolist()]
     samples = n_px * spp * args.steps * n_gpus
     value = samples / (dev_ms * 1e-3) / 1e6
-    mean_img = (total / float(spp * args.steps * n_gpus)).cpu().numpy() if rank == 0 else None
 
     # ---- e2e: through the C-ABI with HOST buffers, every step: camera + lights H2D, result D2H -------
     pinned = torch.empty(n_px * 3, dtype=torch.float32, pin_memory=True)
@@ -359,16 +361,7 @@ def run_b2pt(args, cfg):
     for k in range(args.steps):
         r.SetCameraRaw(pos, iv, ip)
         r.SetLights(scene["lights"])
-        r.ClearAccumulation()
-        r.SetFrameId((k * n_gpus + rank) * spp)
-        if world > 1:
-            r.RenderAccumulate(spp, download=False)
-            dist.reduce(acc, dst=0, op=dist.ReduceOp.SUM)
-            if rank == 0:
-                pinned.copy_(acc.mul(1.0 / (spp * n_gpus)), non_blocking=False)
-            torch.cuda.current_stream().synchronize()
-        else:
-            r.RenderAccumulate(spp, out=host_out)                 # b2pt_render_accumulate: D2H inside the call
+        step(k, 0, out=host_out)
     barrier()
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s], device=f"cuda:{local}", dtype=torch.float64)
@@ -377,18 +370,17 @@ def run_b2pt(args, cfg):
     e2e_value = samples / float(te.item()) / 1e6
     h2d = 12 + 64 + 64 + 24 * len(scene["lights"])
     d2h = n_px * 12
+    mean_img = host_out.copy() if rank == 0 else None     # the last e2e step's image (all ranks' samples)
 
     # ---- attribution pass (untimed): the same steps with one CUDA event after every kernel ---------------
     r.ResetStats()
     r.SetKernelTiming(True)
     n_attr = min(args.steps, 2)
     for k in range(n_attr):
-        r.ClearAccumulation()
-        r.SetFrameId((k * n_gpus + rank) * spp)
-        r.RenderAccumulate(spp, download=False)
+        step(k, 0)
     st_attr = r.Stats()
     r.SetKernelTiming(False)
-    timing_overhead = st_attr["device_ms_render"] / n_attr / max(render_ms / args.steps, 1e-9) - 1.0
+    timing_overhead = st_attr["device_ms_render"] / n_attr / max(st["device_ms_render"] / args.steps, 1e-9) - 1.0
 
     if rank != 0:
         r.close()
@@ -396,7 +388,7 @@ def run_b2pt(args, cfg):
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel (K5 closest-hit traversal) --------------------------------
+    # ---- roofline of the dominant kernel of THIS config --------------------------------------------------
     peaks_path = ROOT / "MEASURED_PEAKS.json"
     if peaks_path.exists():
         peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
@@ -405,33 +397,60 @@ def run_b2pt(args, cfg):
     bpr = algorithmic_bytes_per_ray(scene, w, h, depth, mode, spp=1)
     ms_k, n_k = st_attr["device_ms_kernel"], st_attr["launches_kernel"]
     attr_ms = max(st_attr["device_ms_render"], 1e-9)
-    closest_ms = max(ms_k[0], 1e-9)
-    achieved = st_attr["radiance_rays"] * bpr["closest"] / (closest_ms * 1e-3) / 1e9
-    traffic = None
-    tpath = ROOT / "profiles" / "traffic.json"
-    if tpath.exists():
+    engine_ms, engine_n = st_attr["device_ms_engine"], st_attr["launches_engine"]
+    shares = {"closest": ms_k[0] / attr_ms, "any": ms_k[1] / attr_ms, "surface": ms_k[2] / attr_ms,
+              "shade": ms_k[3] / attr_ms, "other": ms_k[4] / attr_ms, "walk_engine": engine_ms / attr_ms}
+    prof = {}
+    ppath = ROOT / "profiles" / "traffic.json"
+    if ppath.exists():
         try:
-            tj = json.load(open(tpath)).get(args.config, {})
-            traffic = tj.get("k_closest_dram_bytes_per_launch")
-            if traffic is None and tj.get("k_closest_dram_bytes_per_ray") is not None:   # per ray (ncu) x rays of the average launch
-                traffic = tj["k_closest_dram_bytes_per_ray"] * st_attr["radiance_rays"] / max(n_k[0], 1)
+            prof = json.load(open(ppath)).get(args.config, {})
         except Exception:
-            traffic = None
-    roofline = {"kernel": "k_closest (K5 closest-hit BVH traversal)", "bound": "hbm", "achieved": achieved, "peak": peak,
-                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                "bytes_per_ray": bpr["closest"], "nodes_per_ray": bpr["nodes_per_ray"], "tris_per_ray": bpr["tris_per_ray"],
-                "simd_node_loop": bpr["simd_node_loop"], "simd_tri_loop": bpr["simd_tri_loop"],
-                "bytes_per_launch": st_attr["radiance_rays"] * bpr["closest"] / max(n_k[0], 1),
-                "ms_per_launch": closest_ms / max(n_k[0], 1), "launches": n_k[0],
-                "share_of_step": {"closest": ms_k[0] / attr_ms, "any": ms_k[1] / attr_ms, "surface": ms_k[2] / attr_ms,
-                                  "shade": ms_k[3] / attr_ms, "other": ms_k[4] / attr_ms},
-                "attribution": f"separate pass of {n_attr} steps with a CUDA event after every kernel (off while `value` is timed); "
-                               f"that pass ran {timing_overhead * 100:+.2f} % against the timed steps",
-                "shadow": {"achieved": st_attr["shadow_rays_traced"] * bpr["any"] / (max(ms_k[1], 1e-9) * 1e-3) / 1e9,
-                           "bytes_per_ray": bpr["any"]},
-                "note": "algorithmic bytes (nodes + triangles a ray must read) are served by L1/L2 — the README scenes' BVH is "
-                        "16 MB, L2 holds 126 MB — so frac can exceed 1; DRAM sees only the ray/hit I/O (`traffic`, ~40 B/ray). "
-                        "ncu: the kernel's limiter is the L1TEX data pipe (85 % busy), see DESIGN.md section 4"}
+            prof = {}
+    closest_ms = max(ms_k[0], 1e-9)
+    k5 = {"kernel": "k_closest_w (K5 closest-hit BVH traversal)",
+          "achieved": st_attr["radiance_rays"] * bpr["closest"] / (closest_ms * 1e-3) / 1e9, "unit": "GB/s",
+          "bytes_per_ray": bpr["closest"], "nodes_per_ray": bpr["nodes_per_ray"], "tris_per_ray": bpr["tris_per_ray"],
+          "lanes_node_loop": bpr["simd_node_loop"], "lanes_tri_loop": bpr["simd_tri_loop"],
+          "bytes_per_launch": st_attr["radiance_rays"] * bpr["closest"] / max(n_k[0], 1),
+          "ms_per_launch": closest_ms / max(n_k[0], 1), "launches": n_k[0],
+          "dram_bytes_per_ray": prof.get("k_closest_dram_bytes_per_ray"),
+          "shadow": {"achieved": st_attr["shadow_rays_traced"] * bpr["any"] / (max(ms_k[1], 1e-9) * 1e-3) / 1e9,
+                     "bytes_per_ray": bpr["any"]},
+          "limiter": "l1tex wavefronts + dependent-fetch latency: the algorithmic bytes are served by L1/L2 (DRAM sees "
+                     "dram_bytes_per_ray, ncu), so `achieved` against the HBM peak measures work, not a bandwidth bound"}
+    k5["frac"] = k5["achieved"] / peak
+    if engine_ms > max(ms_k[0], ms_k[1]):
+        # the layered walk engine dominates (c4): its algorithmic bytes are the task records it reads and the
+        # partial results it writes — a compute kernel, far from the HBM bound; what limits it is in `limiter`
+        f_hits, s_hits = st_attr["walk_f_hits"], st_attr["walk_s_hits"]
+        eng_bytes = f_hits * 5 * (64 + 12) + s_hits * (48 + 24)
+        achieved = eng_bytes / (engine_ms * 1e-3) / 1e9
+        traffic = prof.get("k_layered_engine_dram_bytes_per_task")
+        roofline = {"kernel": "k_layered_engine (K7d-e, walk engine of the layered BSDF)", "bound": "hbm",
+                    "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": traffic * (5 * f_hits + s_hits) / max(engine_n, 1) if traffic else None,
+                    "peak_source": peak_src, "bytes_per_launch": eng_bytes / max(engine_n, 1),
+                    "ms_per_launch": engine_ms / max(engine_n, 1), "launches": engine_n,
+                    "walk_tasks_per_s": (5 * f_hits + s_hits) / (engine_ms * 1e-3),
+                    "ns_per_shaded_hit": engine_ms * 1e6 / max(s_hits, 1),
+                    "limiter": {"kind": "instruction issue (fp32 ALU / FMA), not memory",
+                                "issue_slots_busy": prof.get("k_layered_engine_issue_active"),
+                                "lanes_per_instruction": prof.get("k_layered_engine_lanes_per_inst"),
+                                "thread_instructions_per_task": prof.get("k_layered_engine_thread_inst_per_task"),
+                                "source": prof.get("k_layered_engine_source", "profiles/ (ncu --set full)")},
+                    "traversal": k5}
+    else:
+        roofline = dict(k5)
+        roofline.update({"bound": "hbm", "peak": peak, "peak_source": peak_src,
+                         "traffic": prof.get("k_closest_dram_bytes_per_launch") or
+                         (prof["k_closest_dram_bytes_per_ray"] * st_attr["radiance_rays"] / max(n_k[0], 1)
+                          if prof.get("k_closest_dram_bytes_per_ray") is not None else None)})
+        if prof.get("k_closest_dram_bytes_per_ray") is not None:
+            roofline["dram_frac"] = prof["k_closest_dram_bytes_per_ray"] * st_attr["radiance_rays"] / (closest_ms * 1e-3) / 1e9 / peak
+    roofline["share_of_step"] = shares
+    roofline["attribution"] = (f"separate pass of {n_attr} steps with a CUDA event after every kernel (off while `value` is "
+                               f"timed); that pass ran {timing_overhead * 100:+.2f} % against the timed steps")
 
     cpu = None
     if n_gpus == 1 and not args.no_cpu_baseline:
@@ -446,10 +465,12 @@ def run_b2pt(args, cfg):
             "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": args.scaling,
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args, cfg, scene),
-            "device": {"rng": "philox", "bvh_nodes": st["n_nodes"], "bvh_build_ms": build_ms,
+            "device": {"rng": "philox", "bvh_nodes": st["n_nodes"], "bvh_wide_nodes": st["n_wide_nodes"],
+                       "bvh_depth": st["bvh_depth"], "bvh_wide_depth": st["bvh_wide_depth"], "bvh_build_ms": build_ms,
                        "scene_device_bytes": st["scene_device_bytes"],
                        "wave_paths_log2": args.wave_log2 or "auto (one wave per step, <= 2^26 paths)",
-                       "parallelism": f"spp-split x{n_gpus}, replicated BVH, one NCCL reduce per step" if n_gpus > 1 else "single GPU"},
+                       "parallelism": (f"spp-split x{n_gpus} ({args.scaling}), replicated BVH, one ncclReduce per step inside "
+                                       "libb2pt.so (b2pt_dist_render_accumulate)") if n_gpus > 1 else "single GPU"},
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "gpu_launches": int(rays[2].item()),
             "mrays_per_s": float(rays[0].item() + rays[1].item()) / (dev_ms * 1e-3) / 1e6,
