@@ -45,6 +45,10 @@ CONFIGS = {
            1024, 1024, 1024, 32, "dielectric"),
     "c4": ("README Layered 1920x1080 1024spp d8", dict(kind="spheres", metallic=0.0), 1920, 1080, 1024, 8, "layered"),
     "c5": ("synthetic 2M-tri mixed 3840x2160 4096spp d8", dict(kind="terrain"), 3840, 2160, 4096, 8, "auto"),
+    # not BASELINE.json configs: the README scene with albedo (alpha cut-out) / normal / metal-rough textures, and the
+    # same scene without them — what the any-hit predicate and the texture fetches cost
+    "tex": ("README scene textured (alpha cut-out) AUTO 1920x1080 1024spp d8", dict(kind="textured"), 1920, 1080, 1024, 8, "auto"),
+    "auto": ("README scene half-metal AUTO 1920x1080 1024spp d8", dict(kind="halfmetal"), 1920, 1080, 1024, 8, "auto"),
 }
 
 
@@ -52,7 +56,13 @@ def make_scene(spec):
     from optixpathtracer_b200 import scenes
     spec = dict(spec)
     kind = spec.pop("kind")
-    return scenes.spheres_scene(**spec) if kind == "spheres" else scenes.terrain_scene()
+    if kind == "spheres":
+        return scenes.spheres_scene(**spec)
+    if kind == "textured":
+        return scenes.textured_spheres_scene(**spec)
+    if kind == "halfmetal":
+        return scenes.halfmetal_spheres_scene(**spec)
+    return scenes.terrain_scene()
 
 
 class ClockSampler:

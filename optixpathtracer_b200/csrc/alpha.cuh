@@ -15,6 +15,8 @@ template <class TexFetch>
 struct AlphaCutout {
     DeviceScene sc;
     TexFetch tex;
+    // meshes without an albedo texture accept every hit: the wide kernels keep their fp32-proof path for them
+    B2PT_HD bool textured(uint32_t mesh) const { return sc.materials[mesh].tex_albedo >= 0; }
     B2PT_HD bool operator()(uint32_t slot, uint32_t mesh, float u, float v) const {
         const int t = sc.materials[mesh].tex_albedo;
         if (t < 0) return true;

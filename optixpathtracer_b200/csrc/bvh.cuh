@@ -58,25 +58,7 @@ constexpr int32_t kEmptyChild = 0x7ffffffe;
 constexpr int kStackSize = 64;
 constexpr int kWideStackSize = 3 * kStackSize;
 
-// The 4-wide node in 64 bytes (what K5/K8 read by default): 4 x LDG.128 per visit instead of 7.  The
-// traversal kernels are bound by L1TEX wavefronts — divergent lanes, one wavefront per lane per load
-// instruction (profiles/r01_k_closest_wide_full_summary.txt: L1TEX 67 % busy, issue 53 %) — so the number
-// of load instructions per visit is what counts.  Child boxes are stored as 8-bit offsets from the node's
-// own origin in units of a power of two per axis:
-//     plane = o + q * 2^(e - 127),   q in [0, 255]
-// rounded OUTWARD in exact arithmetic at build time (K3d), so a quantised box contains the padded fp32 box
-// it stands for and the traversal still only prunes.  Empty slots have child = kEmptyChild (tested by the
-// traversal; their planes are zero).
-struct alignas(16) BvhNode4Q {
-    float ox, oy, oz;                  // origin: low corner of the union of the child boxes
-    uint32_t exps;                     // bytes 0..2: biased exponents e of the x, y, z scales
-    uint32_t qlox, qhix, qloy, qhiy;   // byte k = slot k
-    uint32_t qloz, qhiz, pad0, pad1;
-    int32_t child[4];                  // as BvhNode4
-};
-static_assert(sizeof(BvhNode4Q) == 64, "quantised wide node must be 64 bytes");
-
-// The 4-wide node in 96 bytes, three 256-bit loads per visit (B2PT_STEP=6): the same fp32 boxes, with the four
+// The 4-wide node in 96 bytes, three 256-bit loads per visit (what K5/K8 read by default, B2PT_STEP=6): the same fp32 boxes, with the four
 // child indices hidden in the low mantissa byte of the sixteen x / y planes (child k = the low bytes of
 // lox[k], hix[k], loy[k], hiy[k], least significant first).  K3d rounds each of those planes OUTWARD to a value
 // whose low byte is the payload — at most 511 ulp, 2^-14 relative — so the traversal uses the planes as they

@@ -14,6 +14,7 @@
 //   k_karras       Karras 2012 topology, one thread per internal node
 //   k_refit        bottom-up AABB refit with arrival counters
 //   k_emit_*       leaf-order triangle / normal / uv records and 64-byte nodes
+#include <algorithm>
 #include <cstdlib>
 #include <vector>
 
@@ -319,36 +320,7 @@ __device__ __forceinline__ float slot_area(const Slot4& b) {
     const float dx = b.hx - b.lx, dy = b.hy - b.ly, dz = b.hz - b.lz;
     return dx * dy + dy * dz + dz * dx;
 }
-// One axis of BvhNode4Q: origin o = lowest low plane, scale 2^(e-127) = the smallest power of two with
-// (highest high plane - o) <= 255 steps, planes rounded outward.  fp32 differences and power-of-two
-// divisions are exact in double, so floor / ceil act on the real values.
-__device__ __forceinline__ void quantise_axis(const float lo[4], const float hi[4], const bool used[4], float& o,
-                                              uint32_t& e, uint32_t& qlo, uint32_t& qhi) {
-    float omin = INFINITY, hmax = -INFINITY;
-    for (int k = 0; k < 4; k++)
-        if (used[k]) { omin = fminf(omin, lo[k]); hmax = fmaxf(hmax, hi[k]); }
-    o = omin;
-    const double ext = (double)hmax - (double)omin;
-    int eb = 1;                                            // biased exponent; 2^-126 for a flat axis
-    if (ext > 0.0) {
-        int ex;
-        frexp(ext / 255.0, &ex);                           // ext / 255 = m * 2^ex, m in [0.5, 1)  ->  2^ex >= ext / 255
-        eb = ex + 127;
-        eb = eb < 1 ? 1 : eb;
-    }
-    const double step = ldexp(1.0, eb - 127);
-    e = (uint32_t)eb;
-    qlo = qhi = 0u;
-    for (int k = 0; k < 4; k++) {
-        if (!used[k]) continue;
-        double a = floor(((double)lo[k] - (double)omin) / step);
-        double b = ceil(((double)hi[k] - (double)omin) / step);
-        a = a < 0.0 ? 0.0 : a;
-        b = b > 255.0 ? 255.0 : b;                         // cannot exceed: ext / step <= 255
-        qlo |= (uint32_t)a << (8 * k);
-        qhi |= (uint32_t)b << (8 * k);
-    }
-}
+
 // BvhNode4P: the float nearest to v on the outward side (down: <= v, else >= v) whose low mantissa byte is `payload`.
 __device__ __forceinline__ float embed_byte(float v, uint32_t payload, bool down) {
     const uint32_t u = __float_as_uint(v);
@@ -383,22 +355,6 @@ __device__ __forceinline__ BvhNode4P pack4(const Slot4 sl[4]) {
     p.loy = make_float4(ly[0], ly[1], ly[2], ly[3]); p.hiy = make_float4(hy[0], hy[1], hy[2], hy[3]);
     p.loz = make_float4(lz[0], lz[1], lz[2], lz[3]); p.hiz = make_float4(hz[0], hz[1], hz[2], hz[3]);
     return p;
-}
-__device__ __forceinline__ BvhNode4Q quantise4(const Slot4 sl[4]) {
-    bool used[4];
-    float lo[4], hi[4];
-    BvhNode4Q q;
-    uint32_t ex, ey, ez;
-    for (int k = 0; k < 4; k++) { used[k] = sl[k].child != kEmptyChild; q.child[k] = sl[k].child; }
-    for (int k = 0; k < 4; k++) { lo[k] = sl[k].lx; hi[k] = sl[k].hx; }
-    quantise_axis(lo, hi, used, q.ox, ex, q.qlox, q.qhix);
-    for (int k = 0; k < 4; k++) { lo[k] = sl[k].ly; hi[k] = sl[k].hy; }
-    quantise_axis(lo, hi, used, q.oy, ey, q.qloy, q.qhiy);
-    for (int k = 0; k < 4; k++) { lo[k] = sl[k].lz; hi[k] = sl[k].hz; }
-    quantise_axis(lo, hi, used, q.oz, ez, q.qloz, q.qhiz);
-    q.exps = ex | (ey << 8) | (ez << 16);
-    q.pad0 = q.pad1 = 0u;
-    return q;
 }
 
 __global__ void __launch_bounds__(kThreads)
@@ -461,26 +417,47 @@ k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restric
 // against the traversal stacks (kStackSize, kWideStackSize) instead of trusting it.
 constexpr int kMaxLevels = 128;   // > 63 + 32 (Morton-63 prefix + index tie-break levels, bvh.cuh)
 
-// one level of the sweep: children of the nodes in `fin` are appended to `fout` (order irrelevant: sorted below)
+// one level of the sweep: children of the nodes in `fin` are appended to `fout` (order irrelevant: sorted below),
+// one atomic per warp
 template <bool WIDE>
 __global__ void __launch_bounds__(kThreads)
 k_bfs_level(const BvhNode4* __restrict__ wide, const BvhNode2* __restrict__ nodes, const int* __restrict__ fin,
             int* __restrict__ fout, uint32_t* __restrict__ counts, int L, int* __restrict__ level) {
     const uint32_t n_in = counts[L];
-    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n_in; j += gridDim.x * blockDim.x) {
-        const int i = fin[j];
-        int c[4];
-        if (WIDE) {
-            const int4 ch = *reinterpret_cast<const int4*>(wide[i].child);
-            c[0] = ch.x; c[1] = ch.y; c[2] = ch.z; c[3] = ch.w;
-        } else {
-            c[0] = nodes[i].child0; c[1] = nodes[i].child1; c[2] = c[3] = kEmptyChild;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t iters = (n_in + stride - 1) / stride;
+    for (uint32_t it = 0; it < iters; it++) {
+        const uint32_t j = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        int c[4] = {kEmptyChild, kEmptyChild, kEmptyChild, kEmptyChild};
+        if (j < n_in) {
+            const int i = fin[j];
+            if (WIDE) {
+                const int4 ch = *reinterpret_cast<const int4*>(wide[i].child);
+                c[0] = ch.x; c[1] = ch.y; c[2] = ch.z; c[3] = ch.w;
+            } else {
+                c[0] = nodes[i].child0; c[1] = nodes[i].child1;
+            }
         }
+        uint32_t mine = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) mine += (c[k] >= 0 && c[k] != kEmptyChild) ? 1u : 0u;
+        uint32_t incl = mine;   // inclusive scan over the warp
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= (uint32_t)d) incl += up;
+        }
+        const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+        uint32_t base = 0;
+        if (lane == 31 && total) base = atomicAdd(&counts[L + 1], total);
+        base = __shfl_sync(0xffffffffu, base, 31);
+        uint32_t at = base + incl - mine;
 #pragma unroll
         for (int k = 0; k < 4; k++)
             if (c[k] >= 0 && c[k] != kEmptyChild) {
                 if (level) level[c[k]] = L + 1;
-                fout[atomicAdd(&counts[L + 1], 1u)] = c[k];
+                fout[at++] = c[k];
             }
     }
 }
@@ -504,8 +481,7 @@ k_compact_remap(int n_reach, const uint32_t* __restrict__ order, int* __restrict
 }
 __global__ void __launch_bounds__(kThreads)
 k_compact_emit(int n_reach, const uint32_t* __restrict__ order, const int* __restrict__ remap,
-               const BvhNode4* __restrict__ wide, BvhNode4* __restrict__ out4, BvhNode4Q* __restrict__ outq,
-               BvhNode4P* __restrict__ outp) {
+               const BvhNode4* __restrict__ wide, BvhNode4* __restrict__ out4, BvhNode4P* __restrict__ outp) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n_reach) return;
     const BvhNode4 w = wide[order[j]];
@@ -519,7 +495,6 @@ k_compact_emit(int n_reach, const uint32_t* __restrict__ order, const int* __res
         const int c = w.child[k];
         sl[k].child = (c >= 0 && c != kEmptyChild) ? remap[c] : c;
     }
-    if (outq) outq[j] = quantise4(sl);
     if (outp) outp[j] = pack4(sl);
     if (out4) {
         BvhNode4 o = w;
@@ -585,7 +560,6 @@ DeviceScene SceneBuffers::view() const {
     DeviceScene s;
     s.nodes = nodes.get();
     s.nodes4 = nodes4.get();
-    s.nodes4q = nodes4q.get();
     s.nodes4p = nodes4p.get();
     s.tris = tris.get();
     s.nrms = nrms.get();
@@ -604,7 +578,7 @@ DeviceScene SceneBuffers::view() const {
 }
 
 int64_t SceneBuffers::device_bytes() const {
-    return (int64_t)(nodes.bytes() + nodes4.bytes() + nodes4q.bytes() + nodes4p.bytes() + tris.bytes() + nrms.bytes() + uvs.bytes() + materials.bytes() +
+    return (int64_t)(nodes.bytes() + nodes4.bytes() + nodes4p.bytes() + tris.bytes() + nrms.bytes() + uvs.bytes() + materials.bytes() +
                      textures.bytes() + tri_order.bytes());
 }
 
@@ -719,7 +693,6 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
     out.n_nodes = n == 0 ? 0 : (n == 1 ? 1 : n - 1);
     out.nodes.alloc((size_t)out.n_nodes);
     out.nodes4.release();
-    out.nodes4q.release();
     out.nodes4p.release();
     out.n_wide_nodes = 0;
     out.depth = out.wide_depth = 0;
@@ -832,20 +805,29 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
         d_counts.zero(stream);
         uint32_t* cw = d_counts.get();                     // per-level node counts of the wide tree ...
         uint32_t* cb = d_counts.get() + kMaxLevels + 1;    // ... and of the binary tree (depth only)
+        // levels are enqueued in batches; a batch whose last level came out empty ends the sweep (a balanced tree
+        // of a few million triangles is 12-25 levels deep, kMaxLevels is for the degenerate ones)
         const int sweep_grid = 148 * 2;
-        k_bfs_init<<<1, 1, 0, stream>>>(d_front[0].get(), cw, d_level.get());
-        for (int L = 0; L < kMaxLevels; L++)
-            k_bfs_level<true><<<sweep_grid, kThreads, 0, stream>>>(d_wide.get(), nullptr, d_front[L & 1].get(), d_front[(L + 1) & 1].get(),
-                                                                    cw, L, d_level.get());
-        std::vector<uint32_t> h_counts(2 * (kMaxLevels + 1));
-        if (n > 1) {
-            k_bfs_init<<<1, 1, 0, stream>>>(d_front[0].get(), cb, nullptr);
-            for (int L = 0; L < kMaxLevels; L++)
-                k_bfs_level<false><<<sweep_grid, kThreads, 0, stream>>>(nullptr, out.nodes.get(), d_front[L & 1].get(),
-                                                                         d_front[(L + 1) & 1].get(), cb, L, nullptr);
-        }
-        d_counts.download(h_counts.data(), h_counts.size(), stream);
-        B2PT_CUDA(cudaStreamSynchronize(stream));
+        std::vector<uint32_t> h_counts(2 * (kMaxLevels + 1), 0u);
+        auto sweep = [&](bool is_wide, uint32_t* cnt, uint32_t* h_cnt, int batch) {
+            k_bfs_init<<<1, 1, 0, stream>>>(d_front[0].get(), cnt, is_wide ? d_level.get() : nullptr);
+            for (int L0 = 0; L0 < kMaxLevels; L0 += batch) {
+                const int L1 = std::min(L0 + batch, kMaxLevels);
+                for (int L = L0; L < L1; L++) {
+                    if (is_wide)
+                        k_bfs_level<true><<<sweep_grid, kThreads, 0, stream>>>(d_wide.get(), nullptr, d_front[L & 1].get(),
+                                                                                d_front[(L + 1) & 1].get(), cnt, L, d_level.get());
+                    else
+                        k_bfs_level<false><<<sweep_grid, kThreads, 0, stream>>>(nullptr, out.nodes.get(), d_front[L & 1].get(),
+                                                                                 d_front[(L + 1) & 1].get(), cnt, L, nullptr);
+                }
+                B2PT_CUDA(cudaMemcpyAsync(h_cnt, cnt, (kMaxLevels + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, stream));
+                B2PT_CUDA(cudaStreamSynchronize(stream));
+                if (h_cnt[L1] == 0) break;
+            }
+        };
+        sweep(true, cw, h_counts.data(), 16);
+        if (n > 1) sweep(false, cb, h_counts.data() + kMaxLevels + 1, 32);
         int n_reach = 0;
         for (int L = 0; L <= kMaxLevels; L++) {
             if (h_counts[L]) out.wide_depth = L + 1;
@@ -870,12 +852,11 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
         }
         const uint32_t* worder = d_vals[cur2].get();
         k_compact_remap<<<blocks_for(n_reach), kThreads, 0, stream>>>(n_reach, worder, d_remap.get());
-        const int fmt = trace_wide_formats();   // bit 0: BvhNode4, bit 1: BvhNode4Q, bit 2: BvhNode4P
+        const int fmt = trace_wide_formats();   // bit 0: BvhNode4, bit 2: BvhNode4P
         if (fmt & 1) out.nodes4.alloc((size_t)n_reach);
-        if (fmt & 2) out.nodes4q.alloc((size_t)n_reach);
         if (fmt & 4) out.nodes4p.alloc((size_t)n_reach);
         k_compact_emit<<<blocks_for(n_reach), kThreads, 0, stream>>>(n_reach, worder, d_remap.get(), d_wide.get(),
-                                                                      out.nodes4.get(), out.nodes4q.get(), out.nodes4p.get());
+                                                                      out.nodes4.get(), out.nodes4p.get());
         B2PT_CUDA(cudaGetLastError());
         B2PT_CUDA(cudaStreamSynchronize(stream));   // the temporaries above die with this scope
     }
@@ -888,7 +869,7 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
             B2PT_REQUIRE(3 * out.wide_depth + 1 <= kWideStackSize, B2PT_E_UNSUPPORTED, msg);
         } else {
             snprintf(msg, sizeof msg, "acceleration structure too deep for the traversal stack: %d levels, at most %d "
-                     "(scenes with an alpha-tested texture use the binary-node kernels)", out.depth, kStackSize - 1);
+                     "(binary-node kernels, B2PT_BVH4=0)", out.depth, kStackSize - 1);
             B2PT_REQUIRE(out.depth + 1 <= kStackSize, B2PT_E_UNSUPPORTED, msg);
         }
     }

@@ -44,8 +44,7 @@ struct MeshInfo {
 struct DeviceScene {
     const BvhNode2* nodes;
     const BvhNode4* nodes4;         // the same tree, two levels per node (bvh.cuh)
-    const BvhNode4Q* nodes4q;       // ... and those in 64 bytes, child boxes quantised (B2PT_STEP=2)
-    const BvhNode4P* nodes4p;       // ... and in 96 bytes, child indices hidden in the planes' low bytes (B2PT_STEP=6)
+    const BvhNode4P* nodes4p;       // ... and those in 96 bytes, child indices hidden in the planes' low bytes (B2PT_STEP=6)
     const TriRecord* tris;
     const NrmRecord* nrms;
     const UvRecord* uvs;            // nullptr when no mesh has texcoords
@@ -63,7 +62,6 @@ struct DeviceScene {
 struct SceneBuffers {
     DeviceBuffer<BvhNode2> nodes;
     DeviceBuffer<BvhNode4> nodes4;
-    DeviceBuffer<BvhNode4Q> nodes4q;
     DeviceBuffer<BvhNode4P> nodes4p;
     DeviceBuffer<TriRecord> tris;
     DeviceBuffer<NrmRecord> nrms;
@@ -85,7 +83,7 @@ struct SceneBuffers {
 };
 
 // what the selected traversal kernels need from the build (trace_kernels.cu): wide-node formats they read
-// (bit 0 BvhNode4, bit 1 BvhNode4Q, bit 2 BvhNode4P — the build keeps only those), and whether a scene goes
+// (bit 0 BvhNode4, bit 2 BvhNode4P — the build keeps only those), and whether a scene goes
 // through the wide kernels or the binary ones (decides which stack bound the build checks)
 int trace_wide_formats();
 bool trace_uses_wide(int any_alpha_texture);

@@ -8,7 +8,7 @@
 #include "wavefront.cuh"
 #include "traverse.cuh"
 #include "alpha.cuh"
-#include "trace_wideq.cuh"
+#include "trace_wide.cuh"
 
 #include <cstdlib>
 
@@ -125,17 +125,20 @@ k_closest_d(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active,
     }
 }
 
-// K5 / K8 over the 4-wide nodes (trace_wide.cuh)
-template <bool STATS, int MINB = 4, bool Q = false, int STEP = 0>
+// K5 / K8 over the 4-wide nodes (trace_wide.cuh).  ALPHA: the scene has an alpha cut-out texture (any-hit
+// predicate inside the traversal); SS: stack levels in shared memory
+template <bool STATS, int MINB, int STEP, bool ALPHA, int SS = kSharedStack>
 __global__ void __launch_bounds__(kTraceThreads, MINB)
 k_closest_w(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active, float tmin, float tmax,
             HitRecord* __restrict__ hits, TraceCounters* counters, WarpPolicy pol) {
     TraceStats ts = {0, 0, 0, 0, 0};
     const ClosestIo io{st, hits, tmax};
-    if constexpr (Q)
-        trace_wideq<false, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
+    const void* nodes = STEP == 6 ? (const void*)sc.nodes4p : (const void*)sc.nodes4;
+    if constexpr (ALPHA)
+        trace_wide<false, STATS, STEP, SS>(nodes, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io,
+                                           AlphaCutout<DeviceTexFetch>{sc, DeviceTexFetch{sc.textures}}, ts, pol);
     else
-        trace_wide<false, STATS, STEP>(STEP == 2 ? (const void*)sc.nodes4q : STEP == 6 ? (const void*)sc.nodes4p : (const void*)sc.nodes4, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io, ts, pol);
+        trace_wide<false, STATS, STEP, SS>(nodes, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io, AcceptAllHits(), ts, pol);
     if (STATS) {
         atomicAdd(&counters->nodes, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris, (unsigned long long)ts.tris);
@@ -144,16 +147,18 @@ k_closest_w(DeviceScene sc, PathState st, const uint32_t* __restrict__ n_active,
         atomicAdd(&counters->tri_slots, (unsigned long long)ts.tri_slots);
     }
 }
-template <bool STATS, int MINB = 4, bool Q = false, int STEP = 0>
+template <bool STATS, int MINB, int STEP, bool ALPHA, int SS = kSharedStack>
 __global__ void __launch_bounds__(kTraceThreads, MINB)
 k_any_w(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, float tmin, uint32_t* info,
         uint8_t* occluded, TraceCounters* counters, WarpPolicy pol) {
     TraceStats ts = {0, 0, 0, 0, 0};
     const AnyIo io{sh, info, occluded};
-    if constexpr (Q)
-        trace_wideq<true, STATS>(sc.nodes4, sc.tris, sc.n_nodes, *n_active, tmin, io, ts, pol);
+    const void* nodes = STEP == 6 ? (const void*)sc.nodes4p : (const void*)sc.nodes4;
+    if constexpr (ALPHA)
+        trace_wide<true, STATS, STEP, SS>(nodes, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io,
+                                          AlphaCutout<DeviceTexFetch>{sc, DeviceTexFetch{sc.textures}}, ts, pol);
     else
-        trace_wide<true, STATS, STEP>(STEP == 2 ? (const void*)sc.nodes4q : STEP == 6 ? (const void*)sc.nodes4p : (const void*)sc.nodes4, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io, ts, pol);
+        trace_wide<true, STATS, STEP, SS>(nodes, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io, AcceptAllHits(), ts, pol);
     if (STATS) {
         atomicAdd(&counters->nodes_any, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris_any, (unsigned long long)ts.tris);
@@ -211,44 +216,21 @@ k_any_p(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, fl
     }
 }
 
-// B2PT_TRAVERSAL=0 selects the first (thread-per-ray) kernels, for A/B measurements
-bool use_wide();
-int occ_blocks() {   // resident blocks per SM the traversal kernels are built and launched for
-    static const int v = [] { const char* e = getenv("B2PT_OCC"); return e ? atoi(e) : (use_wide() ? 7 : 8); }();
-    return v;
-}
-WarpPolicy warp_policy() {
-    static const WarpPolicy v = [] {
-        const char* a = getenv("B2PT_REFILL");
-        const char* b = getenv("B2PT_BREAK");
-        const char* q = getenv("B2PT_QBREAK");
-        const char* o = getenv("B2PT_QOUT");
-        int q_out = o ? atoi(o) : 1;
-        q_out = q_out < 1 ? 1 : (q_out > kQMaxOut - 1 ? kQMaxOut - 1 : q_out);
-        const char* sc = getenv("B2PT_SMALL_CHUNKS");
-        const char* au = getenv("B2PT_ANY_UNSORTED");
-        return WarpPolicy{a ? atoi(a) : 8, b ? atoi(b) : 16, q ? atoi(q) : 32, q_out, sc ? atoi(sc) : 1, au ? atoi(au) : 1};
-    }();
-    return v;
-}
-bool use_wide() {   // 4-wide nodes for K5/K8 (scenes without an any-hit predicate); B2PT_BVH4=0: binary nodes
+
+// ---- switches (A/B measurements; the defaults are what the bench runs) ----------------------------
+// B2PT_TRAVERSAL=0 selects the first (thread-per-ray) kernels; B2PT_BVH4=0 the binary-node warp-persistent ones
+// (B2PT_DEFER=0: with the fp64 tests inside K5).  Every variant is bit-exact (tests/test_variants_gpu.py).
+bool use_wide() {
     static const bool v = [] { const char* e = getenv("B2PT_BVH4"); return !(e && e[0] == '0'); }();
     return v;
 }
-// B2PT_STEP selects the node step of trace_wide (all bit-exact, A/B in profiles/r01_ab_node_step.txt):
-// 6 = 96-byte nodes with the child indices in the planes' low mantissa bytes: three 256-bit loads
-// (default); 5 = 128-byte nodes, three 256-bit loads + one 128-bit load of the child indices;
-// 4 = four 256-bit loads (reads the 16 pad bytes too); 3 = warp-cooperative cp.async fetch (slower);
-// 2 = 64-byte quantised nodes (issue-bound, slower); 1 = FMA-form slabs, seven 128-bit loads; 0 = the first step
+// B2PT_STEP: 6 = 96-byte nodes, three 256-bit loads (default); 5 = 128-byte nodes, three 256-bit loads + one
+// 128-bit load of the child indices (profiles/r01_ab_node_step.txt)
 int node_step() {
-    static const int v = [] { const char* e = getenv("B2PT_STEP"); return e ? atoi(e) : 6; }();
+    static const int v = [] { const char* e = getenv("B2PT_STEP"); return e && atoi(e) == 5 ? 5 : 6; }();
     return v;
 }
-bool use_triq() {   // B2PT_TRIQ=1: warp-shared triangle queue (trace_wideq.cuh) — bit-exact, measured 2-5 % slower, kept for A/B
-    static const bool v = [] { const char* e = getenv("B2PT_TRIQ"); return e && e[0] == '1'; }();
-    return v;
-}
-bool use_deferred() {   // B2PT_DEFER=0: fp64 tests inside K5 (trace_persistent), for A/B measurements
+bool use_deferred() {
     static const bool v = [] { const char* e = getenv("B2PT_DEFER"); return !(e && e[0] == '0'); }();
     return v;
 }
@@ -256,86 +238,77 @@ bool use_persistent() {
     static const bool v = [] { const char* e = getenv("B2PT_TRAVERSAL"); return !(e && e[0] == '0'); }();
     return v;
 }
+// B2PT_SSTACK = 16 (default) | 24 | 32: traversal-stack levels of the wide kernels kept in shared memory
+int shared_stack_levels() {
+    static const int v = [] {
+        const char* e = getenv("B2PT_SSTACK");
+        const int n = e ? atoi(e) : kSharedStack;
+        return n == 24 || n == 32 ? n : kSharedStack;
+    }();
+    return v;
+}
+constexpr int kWideOcc = 7;   // resident blocks per SM the wide kernels are built for (A/B: profiles/r01_ab_traversal_occupancy.txt)
+int occ_blocks() {            // ... and the binary ones: B2PT_OCC = 4 | 6 | 8 (default) | 10
+    static const int v = [] { const char* e = getenv("B2PT_OCC"); return e ? atoi(e) : 8; }();
+    return v;
+}
+WarpPolicy warp_policy() {
+    static const WarpPolicy v = [] {
+        const char* a = getenv("B2PT_REFILL");
+        const char* b = getenv("B2PT_BREAK");
+        const char* sc = getenv("B2PT_SMALL_CHUNKS");
+        const char* au = getenv("B2PT_ANY_UNSORTED");
+        return WarpPolicy{a ? atoi(a) : 8, b ? atoi(b) : 16, sc ? atoi(sc) : 1, au ? atoi(au) : 1};
+    }();
+    return v;
+}
 
 }  // namespace
 
-int trace_grid_blocks_per_sm() { return occ_blocks() > 0 ? occ_blocks() : 8; }
+int trace_grid_blocks_per_sm() { return use_persistent() && use_wide() ? kWideOcc : (occ_blocks() > 0 ? occ_blocks() : 8); }
 
+// wide-node formats the build must keep (bit 0 BvhNode4, bit 2 BvhNode4P)
 int trace_wide_formats() {
     if (!(use_persistent() && use_wide())) return 0;
-    if (use_triq()) return 1;
-    return node_step() == 2 ? 2 : node_step() == 6 ? 4 : 1;
+    return node_step() == 6 ? 4 : 1;
 }
-bool trace_uses_wide(int any_alpha_texture) { return use_persistent() && use_wide() && any_alpha_texture == 0; }
+// every scene goes through the wide kernels (the alpha cut-out predicate runs inside them)
+bool trace_uses_wide(int /*any_alpha_texture*/) { return use_persistent() && use_wide(); }
 
-int trace_node_bytes(const DeviceScene& sc) {
-    if (use_persistent() && use_wide() && sc.any_alpha_texture == 0)
-        return use_triq() ? (int)sizeof(BvhNode4) : node_step() == 2 ? (int)sizeof(BvhNode4Q) : node_step() == 6 ? (int)sizeof(BvhNode4P) : (int)sizeof(BvhNode4);
+int trace_node_bytes(const DeviceScene&) {
+    if (use_persistent() && use_wide()) return node_step() == 6 ? (int)sizeof(BvhNode4P) : (int)sizeof(BvhNode4);
     return (int)sizeof(BvhNode2);
 }
+
+#define B2PT_WIDE_ARGS_C <<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy())
+#define B2PT_WIDE_ARGS_A <<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy())
+// the stats build and the alpha build hold more registers: 4 / 6 blocks per SM
+#define B2PT_WIDE_LAUNCH(KERNEL, ARGS)                                                         \
+    do {                                                                                       \
+        const int ss = shared_stack_levels();                                                  \
+        const bool s6 = node_step() == 6;                                                      \
+        if (lc.stats) {                                                                        \
+            if (alpha) { if (s6) KERNEL<true, 4, 6, true> ARGS; else KERNEL<true, 4, 5, true> ARGS; }        \
+            else       { if (s6) KERNEL<true, 4, 6, false> ARGS; else KERNEL<true, 4, 5, false> ARGS; }      \
+        } else if (alpha) {                                                                    \
+            if (s6) KERNEL<false, 6, 6, true> ARGS; else KERNEL<false, 6, 5, true> ARGS;       \
+        } else if (!s6) {                                                                      \
+            KERNEL<false, kWideOcc, 5, false> ARGS;                                            \
+        } else if (ss == 24) {                                                                 \
+            KERNEL<false, kWideOcc, 6, false, 24> ARGS;                                        \
+        } else if (ss == 32) {                                                                 \
+            KERNEL<false, kWideOcc, 6, false, 32> ARGS;                                        \
+        } else {                                                                               \
+            KERNEL<false, kWideOcc, 6, false> ARGS;                                            \
+        }                                                                                      \
+    } while (0)
 
 void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState& st,
                     const uint32_t* n_active, float tmin, float tmax, HitRecord* hits,
                     TraceCounters* counters, bool finish) {
     const bool alpha = sc.any_alpha_texture != 0;
-    if (use_persistent() && use_wide() && !alpha) {
-        const bool tq = use_triq() && sc.n_tris < kQSlotLimit;
-        if (lc.stats && tq)
-            k_closest_w<true, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (tq && occ_blocks() == 8)
-            k_closest_w<false, 8, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (tq && occ_blocks() == 6)
-            k_closest_w<false, 6, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (tq)
-            k_closest_w<false, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (lc.stats && node_step() == 6)
-            k_closest_w<true, 4, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 6 && occ_blocks() == 6)
-            k_closest_w<false, 6, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 6 && occ_blocks() == 7)
-            k_closest_w<false, 7, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 6 && occ_blocks() == 8)
-            k_closest_w<false, 8, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (lc.stats && node_step() == 5)
-            k_closest_w<true, 4, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 5 && occ_blocks() == 6)
-            k_closest_w<false, 6, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 5 && occ_blocks() == 8)
-            k_closest_w<false, 8, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 5 && occ_blocks() == 7)
-            k_closest_w<false, 7, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (lc.stats && node_step() == 4)
-            k_closest_w<true, 4, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 4 && occ_blocks() == 6)
-            k_closest_w<false, 6, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 4 && occ_blocks() == 8)
-            k_closest_w<false, 8, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (lc.stats && node_step() == 3)
-            k_closest_w<true, 4, false, 3><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 3 && occ_blocks() == 6)
-            k_closest_w<false, 6, false, 3><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 3 && occ_blocks() == 8)
-            k_closest_w<false, 8, false, 3><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (lc.stats && node_step() == 2)
-            k_closest_w<true, 4, false, 2><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 2 && occ_blocks() == 6)
-            k_closest_w<false, 6, false, 2><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 2 && occ_blocks() == 8)
-            k_closest_w<false, 8, false, 2><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (lc.stats && node_step() == 1)
-            k_closest_w<true, 4, false, 1><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 1 && occ_blocks() == 6)
-            k_closest_w<false, 6, false, 1><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (node_step() == 1 && occ_blocks() == 8)
-            k_closest_w<false, 8, false, 1><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (lc.stats)
-            k_closest_w<true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (occ_blocks() == 8)
-            k_closest_w<false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (occ_blocks() == 6)
-            k_closest_w<false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else
-            k_closest_w<false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+    if (use_persistent() && use_wide()) {
+        B2PT_WIDE_LAUNCH(k_closest_w, B2PT_WIDE_ARGS_C);
         if (lc.launch_counter) ++*lc.launch_counter;
         if (finish) {
             k_finish_hits<<<lc.grid, 256, 0, lc.stream>>>(sc, st, n_active, hits);
@@ -346,12 +319,10 @@ void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState&
     if (use_persistent() && use_deferred() && !alpha) {
         if (lc.stats)
             k_closest_d<true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (occ_blocks() == 8)
-            k_closest_d<false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (occ_blocks() == 6)
             k_closest_d<false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else
-            k_closest_d<false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+            k_closest_d<false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         if (lc.launch_counter) ++*lc.launch_counter;
         if (finish) {
             k_finish_hits<<<lc.grid, 256, 0, lc.stream>>>(sc, st, n_active, hits);
@@ -366,14 +337,10 @@ void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState&
             k_closest_p<true, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (alpha)
             k_closest_p<false, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (occ_blocks() == 8)
-            k_closest_p<false, false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else if (occ_blocks() == 6)
             k_closest_p<false, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
-        else if (occ_blocks() == 10)
-            k_closest_p<false, false, 10><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         else
-            k_closest_p<false, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
+            k_closest_p<false, false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, st, n_active, tmin, tmax, hits, counters, warp_policy());
         if (lc.launch_counter) ++*lc.launch_counter;
         return;
     }
@@ -392,64 +359,8 @@ void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh
                 const uint32_t* n_active, float tmin, uint32_t* info, uint8_t* occluded,
                 TraceCounters* counters) {
     const bool alpha = sc.any_alpha_texture != 0;
-    if (use_persistent() && use_wide() && !alpha) {
-        const bool tq = use_triq() && sc.n_tris < kQSlotLimit;
-        if (lc.stats && tq)
-            k_any_w<true, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (tq && occ_blocks() == 8)
-            k_any_w<false, 8, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (tq && occ_blocks() == 6)
-            k_any_w<false, 6, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (tq)
-            k_any_w<false, 4, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (lc.stats && node_step() == 6)
-            k_any_w<true, 4, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 6 && occ_blocks() == 6)
-            k_any_w<false, 6, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 6 && occ_blocks() == 7)
-            k_any_w<false, 7, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 6 && occ_blocks() == 8)
-            k_any_w<false, 8, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (lc.stats && node_step() == 5)
-            k_any_w<true, 4, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 5 && occ_blocks() == 6)
-            k_any_w<false, 6, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 5 && occ_blocks() == 8)
-            k_any_w<false, 8, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 5 && occ_blocks() == 7)
-            k_any_w<false, 7, false, 5><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (lc.stats && node_step() == 4)
-            k_any_w<true, 4, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 4 && occ_blocks() == 6)
-            k_any_w<false, 6, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 4 && occ_blocks() == 8)
-            k_any_w<false, 8, false, 4><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (lc.stats && node_step() == 3)
-            k_any_w<true, 4, false, 3><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 3 && occ_blocks() == 6)
-            k_any_w<false, 6, false, 3><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 3 && occ_blocks() == 8)
-            k_any_w<false, 8, false, 3><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (lc.stats && node_step() == 2)
-            k_any_w<true, 4, false, 2><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 2 && occ_blocks() == 6)
-            k_any_w<false, 6, false, 2><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 2 && occ_blocks() == 8)
-            k_any_w<false, 8, false, 2><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (lc.stats && node_step() == 1)
-            k_any_w<true, 4, false, 1><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 1 && occ_blocks() == 6)
-            k_any_w<false, 6, false, 1><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (node_step() == 1 && occ_blocks() == 8)
-            k_any_w<false, 8, false, 1><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (lc.stats)
-            k_any_w<true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (occ_blocks() == 8)
-            k_any_w<false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (occ_blocks() == 6)
-            k_any_w<false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else
-            k_any_w<false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+    if (use_persistent() && use_wide()) {
+        B2PT_WIDE_LAUNCH(k_any_w, B2PT_WIDE_ARGS_A);
         if (lc.launch_counter) ++*lc.launch_counter;
         return;
     }
@@ -460,14 +371,10 @@ void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh
             k_any_p<true, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (alpha)
             k_any_p<false, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (occ_blocks() == 8)
-            k_any_p<false, false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else if (occ_blocks() == 6)
             k_any_p<false, false, 6><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
-        else if (occ_blocks() == 10)
-            k_any_p<false, false, 10><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         else
-            k_any_p<false, false><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
+            k_any_p<false, false, 8><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());
         if (lc.launch_counter) ++*lc.launch_counter;
         return;
     }

@@ -80,8 +80,6 @@ constexpr int kTraceBlock = 128;   // threads per block of the traversal kernels
 struct WarpPolicy {
     int refill_lanes;   // take new rays when this many lanes are idle
     int break_lanes;    // leave the descent when this many lanes cannot descend (hold two leaves / are done)
-    int q_break;        // trace_wideq: ... or when the warp's triangle queue holds this many entries
-    int q_out;          // trace_wideq: leaves a lane may queue and keep descending (1 or 2)
     int small_chunks;   // 1: launches with fewer than 64 rays per warp use smaller chunks (ray_chunk_shift)
     int any_unsorted;   // 1: occlusion rays visit the hit children of a wide node in slot order, not nearest first
 };

@@ -155,6 +155,7 @@ constexpr int kStackSentinel = 0x7fffffff;
 // accepts everything and compiles to nothing; scenes with albedo textures use
 // AlphaCutout (alpha.cuh).
 struct AcceptAllHits {
+    B2PT_HD bool textured(uint32_t /*mesh*/) const { return false; }
     B2PT_HD bool operator()(uint32_t /*slot*/, uint32_t /*mesh*/, float /*u*/, float /*v*/) const { return true; }
 };
 

@@ -3,6 +3,7 @@
 Everything goes through the C-ABI (b2pt_create / b2pt_trace_closest /
 b2pt_trace_any).  Bar: primitive ids, t, u, v bit-exact; occlusion exact.
 """
+import os
 import numpy as np
 import pytest
 
@@ -254,11 +255,24 @@ def test_sliver_chain(oracle):
         _compare(r, oracle, soup, o, d)
 
 
-def test_too_deep_for_the_binary_kernels_is_refused_not_overrun():
-    """Scenes with an alpha-tested texture traverse the binary tree with a 64-entry stack.  A sliver chain down the
-    Morton levels with 2^10 coincident triangles at its end is deeper than that: b2pt_create must say so
-    (B2PT_E_UNSUPPORTED) — or build a tree that fits; it must never build one that does not."""
-    from optixpathtracer_b200._lib import B2ptError
+DEEP_PROG = r'''
+import sys, numpy as np
+sys.path.insert(0, %r)
+from tests.test_trace_gpu import _deep_textured_scene, _renderer
+from optixpathtracer_b200._lib import B2ptError
+try:
+    with _renderer(_deep_textured_scene()) as r:
+        st = r.Stats()
+        assert st["bvh_depth"] + 1 <= 64, st["bvh_depth"]
+        print("DEEP built", st["bvh_depth"])
+except B2ptError as e:
+    assert e.code == -5 and "too deep" in str(e), str(e)
+    print("DEEP refused")
+'''
+
+
+def _deep_textured_scene():
+    """A sliver chain down the Morton levels with 2^10 coincident triangles at its end, on a textured mesh."""
     t = []
     for k in range(1, 22):
         x = 2.0 ** -k
@@ -272,9 +286,20 @@ def test_too_deep_for_the_binary_kernels_is_refused_not_overrun():
     sc["meshes"][0]["texcoords"] = np.zeros((len(soup) * 3, 2), f32)
     sc["meshes"][0]["tex_albedo"] = 0
     sc["textures"] = [np.full((2, 2, 4), 255, np.uint8)]
-    try:
-        with _renderer(sc) as r:
-            st = r.Stats()
-            assert st["bvh_depth"] + 1 <= 64
-    except B2ptError as e:
-        assert e.code == -5 and "too deep" in str(e)
+    return sc
+
+
+def test_too_deep_for_the_binary_kernels_is_refused_not_overrun():
+    """The binary-node kernels (B2PT_BVH4=0) have a 64-entry stack; the binary tree of this scene is deeper than that:
+    b2pt_create must say so (B2PT_E_UNSUPPORTED) — or build a tree that fits; it must never build one that does not.
+    The default (wide) kernels hold it: 3 entries per wide level, 192 entries."""
+    import subprocess, sys
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    env = {k: v for k, v in os.environ.items() if not k.startswith("B2PT_")}
+    env.update({"B2PT_BVH4": "0", "B2PT_NO_REBUILD": "1"})
+    p = subprocess.run([sys.executable, "-c", DEEP_PROG % str(root)], env=env, capture_output=True, text=True, timeout=600, cwd=str(root))
+    assert p.returncode == 0 and "DEEP " in p.stdout, p.stderr[-2000:]
+    with _renderer(_deep_textured_scene()) as r:
+        st = r.Stats()
+        assert 3 * st["bvh_wide_depth"] + 1 <= 192

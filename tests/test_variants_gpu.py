@@ -1,10 +1,11 @@
 """GPU tier: every A/B build variant of the traversal kernels gives the same bits.
 
-The switches (B2PT_STEP, B2PT_TRIQ, B2PT_BVH4, B2PT_DEFER, B2PT_TRAVERSAL, B2PT_SMALL_CHUNKS, B2PT_COLLAPSE, and the
+The switches (B2PT_STEP, B2PT_SSTACK, B2PT_BVH4, B2PT_DEFER, B2PT_OCC, B2PT_TRAVERSAL, B2PT_SMALL_CHUNKS, B2PT_COLLAPSE, and the
 shading-side B2PT_CULL_NEE, B2PT_ENGINE_REFILL, B2PT_ENGINE_OCC — how the layered walk engine hands tasks to lanes) are
 read once per process, so each variant runs in its own subprocess (tests/variant_probe.py): closest hits must
 equal the fp64 brute-force oracle bit for bit, and the occlusion answers, a frame in the reference's random
-sequence and an accumulated Philox image must be identical across variants — and across wave capacities."""
+sequence and an accumulated Philox image must be identical across variants — and across wave capacities.  The
+same for the alpha cut-out scene, whose any-hit predicate runs inside the traversal kernels."""
 import json
 import os
 import subprocess
@@ -18,19 +19,14 @@ ROOT = Path(__file__).resolve().parent.parent
 
 VARIANTS = {
     "default": {},
-    "step0_first_node_step": {"B2PT_STEP": "0"},
-    "step1_fma_slabs": {"B2PT_STEP": "1"},
-    "step2_quantised_nodes": {"B2PT_STEP": "2"},
-    "step3_cooperative_fetch": {"B2PT_STEP": "3"},
-    "step4_four_256bit_loads": {"B2PT_STEP": "4"},
-    "step5_three_256bit_loads_plus_children": {"B2PT_STEP": "5"},
-    "step6_packed_96_byte_nodes": {"B2PT_STEP": "6"},
-    "triangle_queue": {"B2PT_TRIQ": "1"},
+    "step5_128_byte_nodes": {"B2PT_STEP": "5"},
+    "shared_stack_24_levels": {"B2PT_SSTACK": "24"},
+    "shared_stack_32_levels": {"B2PT_SSTACK": "32"},
     "binary_nodes_deferred": {"B2PT_BVH4": "0"},
     "binary_nodes_fp64_in_kernel": {"B2PT_BVH4": "0", "B2PT_DEFER": "0"},
+    "binary_nodes_occupancy_6": {"B2PT_BVH4": "0", "B2PT_OCC": "6"},
     "thread_per_ray": {"B2PT_TRAVERSAL": "0"},
     "fixed_collapse_big_chunks": {"B2PT_COLLAPSE": "fixed", "B2PT_SMALL_CHUNKS": "0"},
-    "occupancy_8": {"B2PT_OCC": "8"},
     "walk_engine_refills_every_idle_lane": {"B2PT_ENGINE_REFILL": "1", "B2PT_ENGINE_OCC": "8"},
     "walk_engine_refills_whole_warps": {"B2PT_ENGINE_REFILL": "32", "B2PT_ENGINE_OCC": "4"},
     "every_shadow_ray_traced": {"B2PT_CULL_NEE": "0"},
@@ -60,10 +56,10 @@ def default_probe():
 def test_variant_gives_the_same_bits(name, default_probe):
     got = default_probe if name == "default" else _probe(VARIANTS[name])
     assert got["closest_equals_oracle"], "closest hits differ from the fp64 brute force"
-    for key in ("any", "frame", "accum_auto"):
+    for key in ("any", "frame", "accum_auto", "closest_textured", "any_textured", "frame_textured"):
         assert got[key] == default_probe[key], f"{key} differs from the default build"
     assert got["accum_small_waves"] == got["accum_auto"], "the image depends on the wave capacity"
-    if name == "step2_quantised_nodes":
-        assert got["node_bytes"] == 64
-    if name == "step6_packed_96_byte_nodes":
+    if name == "default":
         assert got["node_bytes"] == 96
+    if name == "step5_128_byte_nodes":
+        assert got["node_bytes"] == 128

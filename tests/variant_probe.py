@@ -43,6 +43,17 @@ def main():
         out["accum_auto"] = hashlib.sha256(r.RenderAccumulate(6).tobytes()).hexdigest()
         st = r.Stats()
         out["node_bytes"] = st["node_bytes"]
+    # the alpha cut-out scene: the any-hit predicate runs inside whichever traversal kernel the variant selects
+    # (the thread-per-ray and binary-node variants are the first implementation, pinned against the reference's
+    # frames in tests/test_render_gpu.py; the others must give their bits)
+    tx = cases.frame_scenes()["textured"]
+    with OptixRenderer(None, tx, bsdf_mode="auto", rng_mode="lcg_host", max_bounces=cases.FRAME_BOUNCES) as r:
+        r.Resize((w, h)); r.SetCamera(tx["camera"]); r.SetLights(tx["lights"])
+        prim, _, t, u, v = r.TraceClosest(o, d)
+        out["closest_textured"] = hashlib.sha256(prim.tobytes() + t.tobytes() + u.tobytes() + v.tobytes()).hexdigest()
+        occ = r.TraceAny(o, d, np.full(len(o), 3.0, dtype=np.float32))
+        out["any_textured"] = hashlib.sha256(np.asarray(occ).tobytes()).hexdigest()
+        out["frame_textured"] = hashlib.sha256(r.Render().tobytes()).hexdigest()
     with OptixRenderer(None, sc, bsdf_mode="auto", rng_mode="philox", max_bounces=cases.FRAME_BOUNCES,
                        wave_paths_log2=12) as r:   # many small waves
         r.Resize((w, h)); r.SetCamera(sc["camera"]); r.SetLights(sc["lights"])
