@@ -321,7 +321,9 @@ int b2pt_trace_any(B2ptRenderer* r, int64_t n, const float* org, const float* di
  * shading space, z = normal).  `seed` is the LCG state on entry (rng policy
  * = lcg_mode, B2PT_RNG_LCG_DEVICE or _HOST); seed_out (may be NULL) is the
  * state on return, so draw counts are checked too.
- * lcg_mode = B2PT_RNG_PHILOX with bsdf = B2PT_BSDF_LAYERED runs the per-lane
+ * lcg_mode = B2PT_RNG_PHILOX is the production instantiation: the same
+ * functions drawing from Philox keyed (seed[i], row); seed_out is zeroed.
+ * With bsdf = B2PT_BSDF_LAYERED it runs the per-lane
  * logic of the production walk engine instead (csrc/fast_layered.cuh): seed
  * keys the Philox streams, seed_out is zeroed, and `sample` reports
  * f = weight / |wi.z| with pdf = 1 (the engine only forms f |cos| / pdf).

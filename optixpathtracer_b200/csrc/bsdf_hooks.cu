@@ -47,10 +47,10 @@ int hook_guard(int device, F&& f) {
 }
 
 bool bad_bsdf(int b) { return b < B2PT_BSDF_CONDUCTOR || b > B2PT_BSDF_LAYERED; }
-// rng PHILOX selects the production walk engine's per-lane logic (fast_layered.cuh); only the layered BSDF has one
-bool bad_lcg(int m, int bsdf) {
-    if (m == B2PT_RNG_PHILOX) return bsdf != B2PT_BSDF_LAYERED;
-    return m != B2PT_RNG_LCG_DEVICE && m != B2PT_RNG_LCG_HOST;
+// rng PHILOX = the production instantiation: for the layered BSDF the walk engine's per-lane logic
+// (fast_layered.cuh), for the others the same bsdf.cuh functions drawing from PhiloxRng as K7 does
+bool bad_lcg(int m, int /*bsdf*/) {
+    return m != B2PT_RNG_PHILOX && m != B2PT_RNG_LCG_DEVICE && m != B2PT_RNG_LCG_HOST;
 }
 int blocks(int64_t n) { return (int)((n + 127) / 128); }
 
@@ -74,8 +74,10 @@ int b2pt_bsdf_f(int32_t device, int32_t bsdf, int32_t lcg_mode, int64_t n, const
         d_s.upload(seed, (size_t)n);
         d_f.alloc((size_t)n * 3); d_so.alloc((size_t)n);
         d_so.zero();
-        if (lcg_mode == B2PT_RNG_PHILOX)
+        if (lcg_mode == B2PT_RNG_PHILOX && bsdf == B2PT_BSDF_LAYERED)
             launch_fast_layered_rows_f(n, d_a.get(), d_r.get(), d_wo.get(), d_wi.get(), d_s.get(), d_f.get());
+        else if (lcg_mode == B2PT_RNG_PHILOX)
+            k_bsdf_f<PhiloxRng><<<blocks(n), 128>>>(bsdf, n, d_a.get(), d_r.get(), d_wo.get(), d_wi.get(), d_s.get(), d_f.get(), d_so.get());
         else if (lcg_mode == B2PT_RNG_LCG_HOST)
             k_bsdf_f<LcgRng<true>><<<blocks(n), 128>>>(bsdf, n, d_a.get(), d_r.get(), d_wo.get(), d_wi.get(), d_s.get(), d_f.get(), d_so.get());
         else
@@ -102,9 +104,11 @@ int b2pt_bsdf_sample(int32_t device, int32_t bsdf, int32_t lcg_mode, int64_t n, 
         d_f.alloc((size_t)n * 3); d_wi.alloc((size_t)n * 3); d_p.alloc((size_t)n);
         d_so.alloc((size_t)n); d_ok.alloc((size_t)n); d_fl.alloc((size_t)n);
         d_so.zero();
-        if (lcg_mode == B2PT_RNG_PHILOX)
+        if (lcg_mode == B2PT_RNG_PHILOX && bsdf == B2PT_BSDF_LAYERED)
             launch_fast_layered_rows_sample(n, d_a.get(), d_r.get(), d_wo.get(), d_s.get(), d_ok.get(), d_f.get(), d_wi.get(),
                                             d_p.get(), d_fl.get());
+        else if (lcg_mode == B2PT_RNG_PHILOX)
+            k_bsdf_sample<PhiloxRng><<<blocks(n), 128>>>(bsdf, n, d_a.get(), d_r.get(), d_wo.get(), d_s.get(), d_ok.get(), d_f.get(), d_wi.get(), d_p.get(), d_fl.get(), d_so.get());
         else if (lcg_mode == B2PT_RNG_LCG_HOST)
             k_bsdf_sample<LcgRng<true>><<<blocks(n), 128>>>(bsdf, n, d_a.get(), d_r.get(), d_wo.get(), d_s.get(), d_ok.get(), d_f.get(), d_wi.get(), d_p.get(), d_fl.get(), d_so.get());
         else

@@ -9,6 +9,19 @@
 
 namespace b2pt {
 
+// the generator of a row: the LCG policies start from the row's 32-bit state and report it back; the production
+// generator is keyed the way a render keys it, with (seed, pixel, sample) = (seed[i], 0, row), and reports 0
+template <class Rng>
+struct RowRng {
+    static B2PT_HD Rng open(uint32_t seed, int64_t) { return Rng(seed); }
+    static B2PT_HD uint32_t close(const Rng& r) { return r.s; }
+};
+template <>
+struct RowRng<PhiloxRng> {
+    static B2PT_HD PhiloxRng open(uint32_t seed, int64_t i) { return PhiloxRng((uint64_t)seed, 0u, (uint32_t)i, 0u); }
+    static B2PT_HD uint32_t close(const PhiloxRng&) { return 0u; }
+};
+
 // bsdf = B2PT_BSDF_CONDUCTOR .. B2PT_BSDF_LAYERED (1..4)
 template <class Rng>
 B2PT_HD void bsdf_row_f(int bsdf, int64_t i, const float* albedo, const float* roughness, const float* wo,
@@ -16,7 +29,7 @@ B2PT_HD void bsdf_row_f(int bsdf, int64_t i, const float* albedo, const float* r
     const ShadePoint sp = {v3(albedo[3 * i], albedo[3 * i + 1], albedo[3 * i + 2]), roughness[i]};
     const float3 o = v3(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]);
     const float3 in = v3(wi[3 * i], wi[3 * i + 1], wi[3 * i + 2]);
-    Rng rng(seed ? seed[i] : 0u);
+    Rng rng = RowRng<Rng>::open(seed ? seed[i] : 0u, i);
     float3 f = v3(0.0f);
     switch (bsdf) {
         case B2PT_BSDF_CONDUCTOR: f = bsdf_f<kBsdfConductor>(rng, sp, o, in); break;
@@ -28,7 +41,7 @@ B2PT_HD void bsdf_row_f(int bsdf, int64_t i, const float* albedo, const float* r
     f_out[3 * i] = f.x;
     f_out[3 * i + 1] = f.y;
     f_out[3 * i + 2] = f.z;
-    if (seed_out) seed_out[i] = rng.s;
+    if (seed_out) seed_out[i] = RowRng<Rng>::close(rng);
 }
 
 template <class Rng>
@@ -37,7 +50,7 @@ B2PT_HD void bsdf_row_sample(int bsdf, int64_t i, const float* albedo, const flo
                              uint8_t* flags_out, uint32_t* seed_out) {
     const ShadePoint sp = {v3(albedo[3 * i], albedo[3 * i + 1], albedo[3 * i + 2]), roughness[i]};
     const float3 o = v3(wo[3 * i], wo[3 * i + 1], wo[3 * i + 2]);
-    Rng rng(seed[i]);
+    Rng rng = RowRng<Rng>::open(seed[i], i);
     BsdfSample s;
     s.f = s.wi = v3(0.0f);
     s.pdf = 0.0f;
@@ -59,7 +72,7 @@ B2PT_HD void bsdf_row_sample(int bsdf, int64_t i, const float* albedo, const flo
     wi_out[3 * i + 2] = good ? s.wi.z : 0.0f;
     pdf_out[i] = good ? s.pdf : 0.0f;
     flags_out[i] = good ? (uint8_t)s.flags : 0;
-    if (seed_out) seed_out[i] = rng.s;
+    if (seed_out) seed_out[i] = RowRng<Rng>::close(rng);
 }
 
 // ---- rows of the production (Philox) walk engine, fast_layered.cuh: one whole shade per row --------------------

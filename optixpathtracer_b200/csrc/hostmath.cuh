@@ -20,6 +20,14 @@
 // the library, minus errno).  The shading translation units are built with
 // -fmad=false, so the doubles below are rounded after every operation as in the
 // library's non-FMA build.
+//
+// Provenance of the constants: bit parity with the library REQUIRES the library's own numbers, so the polynomial
+// coefficients, the pi/2 reduction constants and the 32-entry exp table below are numerically identical to the data
+// of the Arm Optimized Routines single-precision sinf / cosf / expf (math/sincosf_data.c `__sincosf_table`,
+// math/exp2f_data.c `__exp2f_data`; Copyright (c) Arm Limited, SPDX-License-Identifier: MIT OR Apache-2.0 WITH
+// LLVM-exception), the same data glibc >= 2.28 ships in sysdeps/ieee754/flt-32/ under the LGPL-2.1-or-later.  They
+// are mathematical constants (minimax coefficients; T[i] = bits(2^(i/32)) - (i << 47)); the code around them is
+// written here against the algorithm's description, not transcribed.
 #pragma once
 
 #include "vecmath.cuh"

@@ -56,7 +56,7 @@ struct DeviceScene {
     int32_t n_meshes;
     int32_t n_textures;
     int32_t any_alpha_texture;      // some mesh has an albedo texture (any-hit cut-out, A9)
-    float max_abs;                  // largest |coordinate| of the geometry (the boxes are padded by 2^-18 of it)
+    float max_abs;                  // largest |coordinate| of the geometry (the boxes are padded by 2^-17 of it)
 };
 
 struct SceneBuffers {

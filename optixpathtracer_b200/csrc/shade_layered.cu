@@ -25,9 +25,11 @@ namespace b2pt {
 namespace {
 
 constexpr uint32_t kNoF = 0xffffffffu;
-// K7d-p / K7d-f are gather / scatter kernels bound by memory latency (ncu: 12-16 % of the issue slots used):
-// they are built for the full 2048 threads per SM
-constexpr int kPrepOcc = 16;
+// K7d-p / K7d-f are gather / scatter kernels bound by memory latency (ncu: 12-16 % of the issue slots used), but more
+// resident threads do not help them: built for 16 blocks per SM (32 registers, 28-40 bytes of spills) they were 10-30 %
+// SLOWER (prep 0.78 -> 1.02 ms, finish 1.50 -> 1.66 ms per c4 launch, c4 573 -> 549 Msamples/s,
+// profiles/r02_ab_prep_finish_occupancy.txt): the grid stays at 8 blocks per SM with the registers the compiler wants
+constexpr int kPrepGrid = 8;
 
 // scratch of one bounce, `capacity` slots per plane (B2ptRenderer::d_layered)
 // task record of one hit, 64 bytes, written by K7d-p and read by every walk task of the hit (the five f walks of
@@ -60,7 +62,7 @@ __device__ __forceinline__ fastlayer::WalkKey task_key(const WaveParams& wp, uin
 }
 
 // ---- K7d-p -------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kWaveThreads, kPrepOcc)
+__global__ void __launch_bounds__(kWaveThreads)
 k_layered_prep(WaveParams wp, PathState st, SurfaceState sf, LayeredScratch ls, const uint32_t* __restrict__ lq,
                const uint32_t* __restrict__ queued, uint32_t* __restrict__ lcounts, uint32_t bounce) {
     const uint32_t n = queued[4 * bounce + kBsdfLayered];
@@ -178,7 +180,7 @@ k_layered_engine(LayeredScratch ls, const uint32_t* __restrict__ lq, const uint3
 }
 
 // ---- K7d-f -------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kWaveThreads, kPrepOcc)
+__global__ void __launch_bounds__(kWaveThreads)
 k_layered_finish(WaveParams wp, PathState st, PathState nx, SurfaceState sf, LayeredScratch ls,
                  const uint32_t* __restrict__ lq, WaveCounts wc, const uint32_t* __restrict__ lcounts, uint32_t bounce,
                  float* __restrict__ wave_out, TraceCounters* __restrict__ counters) {
@@ -295,7 +297,7 @@ void launch_layered_prep(B2ptRenderer* r, const WaveParams& wp, const PathState&
                          uint32_t* lcounts, uint32_t bounce) {
     const LayeredScratch ls = scratch_view(r, wp.capacity);
     const uint32_t* lq = r->d_queues.get() + (size_t)kBsdfLayered * wp.capacity;
-    k_layered_prep<<<r->sm_count * kPrepOcc, kWaveThreads, 0, r->stream>>>(wp, cur, r->surf, ls, lq, wc.queued, lcounts, bounce);
+    k_layered_prep<<<r->sm_count * kPrepGrid, kWaveThreads, 0, r->stream>>>(wp, cur, r->surf, ls, lq, wc.queued, lcounts, bounce);
 }
 
 void launch_layered_walks(B2ptRenderer* r, const WaveParams& wp, const WaveCounts& wc, uint32_t* lcounts, uint32_t bounce) {
@@ -325,7 +327,7 @@ void launch_layered_finish(B2ptRenderer* r, const WaveParams& wp, const PathStat
                            const WaveCounts& wc, const uint32_t* lcounts, uint32_t bounce) {
     const LayeredScratch ls = scratch_view(r, wp.capacity);
     const uint32_t* lq = r->d_queues.get() + (size_t)kBsdfLayered * wp.capacity;
-    k_layered_finish<<<r->sm_count * kPrepOcc, kWaveThreads, 0, r->stream>>>(wp, cur, nxt, r->surf, ls, lq, wc, lcounts, bounce,
+    k_layered_finish<<<r->sm_count * kPrepGrid, kWaveThreads, 0, r->stream>>>(wp, cur, nxt, r->surf, ls, lq, wc, lcounts, bounce,
                                                                        r->d_wave_out.get(), r->d_counters.get());
 }
 

@@ -22,8 +22,8 @@ namespace b2pt {
 
 // Slab test of slot k of a wide node with one FMA per plane: t = plane * (1/d) - o * (1/d), the second product rounded once per
 // ray.  Its rounding error, <= 2^-24 |o| in position units, is absolute, not relative like the errors
-// tf * 1.000001f covers; the boxes' outward padding (2^-18 of the scene's largest coordinate M, K3) absorbs it
-// with a factor 4 to spare while |o| <= 16 M.  Rays that start farther out (a distant camera) carry the bound
+// tf * 1.000001f covers; the boxes' outward padding (2^-17 of the scene's largest coordinate M, bvh_build.cu) absorbs it
+// with a factor 8 to spare while |o| <= 16 M.  Rays that start farther out (a distant camera) carry the bound
 // as explicit slack, eslack = 2^-22 max_i |o_i / d_i| (0 otherwise) — correct for them too, only less tight.
 #define B2PT_SLAB4F(k, comp)                                                                                  \
     {                                                                                                         \

@@ -36,7 +36,7 @@ struct TraceStats {
 };
 
 // fp64 Moeller-Trumbore, the deciding test.  Operation order is part of the
-// contract (oracle/oracle_port.cpp::exact_triangle mirrors it).
+// contract (oracle/exact_tri.h::exact_triangle, used by oracle/oracle_trace.cpp, mirrors it).
 B2PT_HD bool tri_exact(float3 of, float3 df, float3 v0f, float3 v1f, float3 v2f,
                        double& t, double& u, double& v, bool& backface) {
     const double ox = of.x, oy = of.y, oz = of.z;

@@ -138,6 +138,47 @@ def spheres_scene(metallic: float = 0.0, segments: int = 64, rings: int = 32,
             "camera": scene1_camera()}
 
 
+def textured_spheres_scene(n: int = 64, **kw):
+    """The README scene with what a glTF export of it usually carries: every other sphere has an albedo texture with
+    alpha cut-out holes (the any-hit predicate, devicePrograms.cu:518-561), every third a normal map, every fourth
+    a metal-rough map; half of the spheres are metallic, so AUTO mode mixes conductor and layered."""
+    sc = spheres_scene(**kw)
+    yy, xx = np.mgrid[0:n, 0:n]
+    alb = np.zeros((n, n, 4), dtype=np.uint8)
+    c = ((xx // 4 + yy // 4) % 2).astype(np.uint8)
+    alb[..., 0] = 60 + 180 * c
+    alb[..., 1] = 200 - 120 * c
+    alb[..., 2] = 90 + (xx * 3) % 160
+    alb[..., 3] = np.where((xx % 8 < 2) & (yy % 8 < 2), 40, 255)   # 1/16 of the surface is cut out
+    nm = np.zeros((n, n, 4), dtype=np.uint8)
+    nm[..., 0] = 128 + (20 * np.sin(xx * 0.4)).astype(np.int32)
+    nm[..., 1] = 128 + (20 * np.cos(yy * 0.4)).astype(np.int32)
+    nm[..., 2] = 235
+    nm[..., 3] = 255
+    mr = np.zeros((n, n, 4), dtype=np.uint8)
+    mr[..., 0] = np.where((xx // 4 + yy // 4) % 2 == 0, 255, 0)
+    mr[..., 1] = 40 + 10 * ((xx * 3 + yy) % 16)
+    mr[..., 3] = 255
+    sc["textures"] = [alb, nm, mr]
+    for k, me in enumerate(sc["meshes"][:36]):
+        me["metallic"] = float(k % 2)
+        if k % 2 == 0:
+            me["tex_albedo"] = 0
+        if k % 3 == 0:
+            me["tex_normal"] = 1
+        if k % 4 == 0:
+            me["tex_metal_rough"] = 2
+    return sc
+
+
+def halfmetal_spheres_scene(**kw):
+    """textured_spheres_scene without its textures: the untextured AUTO-mode comparison point."""
+    sc = spheres_scene(**kw)
+    for k, me in enumerate(sc["meshes"][:36]):
+        me["metallic"] = float(k % 2)
+    return sc
+
+
 def _value_noise(nx, ny, seed, octaves=3):
     """SplitMix64-seeded value noise on an (ny, nx) grid, deterministic."""
     def splitmix(n, s):

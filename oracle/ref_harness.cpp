@@ -20,7 +20,7 @@
 //     source (commented lines devicePrograms.cu:304-307, 324-327).  ref_mode_*
 //     below restates __closesthit__radiance with exactly those lines switched
 //     in; in AUTO mode the restatement is checked bit-for-bit against the
-//     unmodified program (tests/test_ref_oracle.py).
+//     unmodified program (tests/test_bsdf_cpu.py::test_ref_oracle_reproduces_goldens).
 //   * hasNormalTexture / hasMetalRoughTexture are set from their own texture
 //     ids (the reference copies HasAlbedoTex() into all three,
 //     OptixRenderer.cpp:535,540 — SURVEY Q4, documented FIX).

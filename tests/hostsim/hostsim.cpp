@@ -190,10 +190,12 @@ void hostsim_bsdf_f(int bsdf, int lcg_mode, int64_t n, const float* albedo, cons
                     const float* wo, const float* wi, const uint32_t* seed, float* f_out, uint32_t* seed_out) {
 #pragma omp parallel for schedule(static)
     for (int64_t i = 0; i < n; i++) {
-        if (lcg_mode == B2PT_RNG_PHILOX) {   // the production walk engine (layered only)
+        if (lcg_mode == B2PT_RNG_PHILOX && bsdf == B2PT_BSDF_LAYERED) {   // the production walk engine
             fast_layered_row_f(i, albedo, roughness, wo, wi, seed, f_out);
             if (seed_out) seed_out[i] = 0u;
-        } else if (lcg_mode == B2PT_RNG_LCG_HOST)
+        } else if (lcg_mode == B2PT_RNG_PHILOX)
+            bsdf_row_f<PhiloxRng>(bsdf, i, albedo, roughness, wo, wi, seed, f_out, seed_out);
+        else if (lcg_mode == B2PT_RNG_LCG_HOST)
             bsdf_row_f<LcgRng<true>>(bsdf, i, albedo, roughness, wo, wi, seed, f_out, seed_out);
         else
             bsdf_row_f<LcgRng<false>>(bsdf, i, albedo, roughness, wo, wi, seed, f_out, seed_out);
@@ -205,10 +207,12 @@ void hostsim_bsdf_sample(int bsdf, int lcg_mode, int64_t n, const float* albedo,
                          float* pdf_out, uint8_t* flags_out, uint32_t* seed_out) {
 #pragma omp parallel for schedule(static)
     for (int64_t i = 0; i < n; i++) {
-        if (lcg_mode == B2PT_RNG_PHILOX) {
+        if (lcg_mode == B2PT_RNG_PHILOX && bsdf == B2PT_BSDF_LAYERED) {
             fast_layered_row_sample(i, albedo, roughness, wo, seed, ok, f_out, wi_out, pdf_out, flags_out);
             if (seed_out) seed_out[i] = 0u;
-        } else if (lcg_mode == B2PT_RNG_LCG_HOST)
+        } else if (lcg_mode == B2PT_RNG_PHILOX)
+            bsdf_row_sample<PhiloxRng>(bsdf, i, albedo, roughness, wo, seed, ok, f_out, wi_out, pdf_out, flags_out, seed_out);
+        else if (lcg_mode == B2PT_RNG_LCG_HOST)
             bsdf_row_sample<LcgRng<true>>(bsdf, i, albedo, roughness, wo, seed, ok, f_out, wi_out, pdf_out,
                                           flags_out, seed_out);
         else
