@@ -316,6 +316,19 @@ int b2pt_trace_closest(B2ptRenderer* r, int64_t n, const float* org, const float
  * occluded[i] = 1 iff some triangle has tmin < t < tmax[i].                 */
 int b2pt_trace_any(B2ptRenderer* r, int64_t n, const float* org, const float* dir,
                    float tmin, const float* tmax, uint8_t* occluded);
+/* b2pt_trace_any for callers that cannot allocate (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  No
+ * counterpart in the reference.
+ * Same arguments, same kernel, same answers; the ray planes, the ray count
+ * and the answers live in one file-scope __device__ array (csrc/noalloc.cu,
+ * 1.7 MB held by every GPU that loads the library until exit) instead of
+ * per-call cudaMalloc'ed buffers, and the call makes no cudaMalloc / cudaFree
+ * / allocating library call.  n > B2PT_NOALLOC_MAX_RAYS returns
+ * B2PT_E_UNSUPPORTED (b2pt_last_error says so).  Every call on a device
+ * shares the array: calls that overlap on one GPU race — serialise them.   */
+#define B2PT_NOALLOC_MAX_RAYS 32768
+int b2pt_trace_any_noalloc(B2ptRenderer* r, int64_t n, const float* org, const float* dir,
+                           float tmin, const float* tmax, uint8_t* occluded);
 
 /* BSDF device functions, one thread per row (PBRT/ headers, all in local
  * shading space, z = normal).  `seed` is the LCG state on entry (rng policy

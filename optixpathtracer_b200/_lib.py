@@ -107,6 +107,7 @@ SIGNATURES = {
     "b2pt_trace_closest": (C.c_int, [_H, C.c_int64, c_float_p, c_float_p, C.c_float, C.c_float,
                                       c_int32_p, c_int32_p, c_float_p, c_float_p, c_float_p]),
     "b2pt_trace_any": (C.c_int, [_H, C.c_int64, c_float_p, c_float_p, C.c_float, c_float_p, c_uint8_p]),
+    "b2pt_trace_any_noalloc": (C.c_int, [_H, C.c_int64, c_float_p, c_float_p, C.c_float, c_float_p, c_uint8_p]),
     "b2pt_bsdf_f": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, c_float_p, c_float_p,
                                c_float_p, c_float_p, c_uint32_p, c_float_p, c_uint32_p]),
     "b2pt_bsdf_sample": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_int64, c_float_p, c_float_p,

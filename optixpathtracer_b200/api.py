@@ -278,6 +278,20 @@ class OptixRenderer:
                                                occ.ctypes.data_as(_lib.c_uint8_p)))
         return occ
 
+    NOALLOC_MAX_RAYS = 32768   # B2PT_NOALLOC_MAX_RAYS (include/b2pt.h)
+
+    def TraceAnyNoAlloc(self, org, dirs, tmax, tmin: float = 0.0):
+        """b2pt_trace_any_noalloc: TraceAny through the library's static device scratch — no cudaMalloc in the
+        call, at most NOALLOC_MAX_RAYS rays, calls on one GPU must not overlap."""
+        o = np.ascontiguousarray(org, dtype=f32).reshape(-1, 3)
+        d = np.ascontiguousarray(dirs, dtype=f32).reshape(-1, 3)
+        n = o.shape[0]
+        tm = np.ascontiguousarray(np.broadcast_to(np.asarray(tmax, dtype=f32), (n,)), dtype=f32)
+        occ = np.empty(n, dtype=np.uint8)
+        check(self._h, self.lib.b2pt_trace_any_noalloc(self._h, n, _fp(o), _fp(d), tmin, _fp(tm),
+                                                       occ.ctypes.data_as(_lib.c_uint8_p)))
+        return occ
+
     def DownloadBvh(self):
         st = self.Stats()
         # the binary (64-byte) nodes the builder emits; the 4-wide nodes K5/K8 walk are derived from them
