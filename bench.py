@@ -459,6 +459,8 @@ def run_b2pt(args, cfg):
         if prof.get("k_closest_dram_bytes_per_ray") is not None:
             roofline["dram_frac"] = prof["k_closest_dram_bytes_per_ray"] * st_attr["radiance_rays"] / (closest_ms * 1e-3) / 1e9 / peak
     roofline["share_of_step"] = shares
+    roofline["ms_per_step_by_class"] = {"closest": ms_k[0] / n_attr, "any": ms_k[1] / n_attr, "surface": ms_k[2] / n_attr,
+                                        "shade": ms_k[3] / n_attr, "other": ms_k[4] / n_attr, "walk_engine": engine_ms / n_attr}
     roofline["attribution"] = (f"separate pass of {n_attr} steps with a CUDA event after every kernel (off while `value` is "
                                f"timed); that pass ran {timing_overhead * 100:+.2f} % against the timed steps")
 

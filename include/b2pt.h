@@ -118,7 +118,7 @@ typedef struct B2ptConfig {
     uint64_t seed;            /* Philox key; ignored by the LCG modes             */
     int32_t  max_bounces;     /* main.cpp:87 uses 2; b2pt default 8               */
     int32_t  wave_paths_log2; /* in-flight paths per wavefront (log2), 0 = auto   */
-    int32_t  bvh_leaf_size;   /* reserved, 0 = auto                               */
+    int32_t  bvh_leaf_size;   /* triangles per leaf of the wide tree, 1..8; 0 = 2 */
     int32_t  collect_stats;   /* 1 = count nodes/triangles per ray (slower)       */
 } B2ptConfig;
 

@@ -77,7 +77,7 @@ class OptixRenderer:
 
     def __init__(self, ptx_path: str | None, model: dict, *, device: int = 0,
                  bsdf_mode="auto", rng_mode="philox", seed: int = 0x5EED, max_bounces: int = 8,
-                 wave_paths_log2: int = 0, collect_stats: bool = False):
+                 wave_paths_log2: int = 0, collect_stats: bool = False, bvh_leaf_size: int = 0):
         self.lib = _lib.load()
         self.model = model
         cfg = B2ptConfig()
@@ -89,6 +89,7 @@ class OptixRenderer:
         cfg.max_bounces = max_bounces
         cfg.wave_paths_log2 = wave_paths_log2
         cfg.collect_stats = int(collect_stats)
+        cfg.bvh_leaf_size = bvh_leaf_size      # triangles per leaf of the wide tree, 0 = default (2)
         marshal = _SceneMarshal(model)
         h = C.c_void_p()
         rc = self.lib.b2pt_create(C.byref(marshal.desc), C.byref(cfg), C.byref(h))

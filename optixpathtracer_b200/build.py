@@ -41,7 +41,7 @@ NVCC_FLAGS = [
 # The walk engine of the production (Philox) generator is not bit-compatible with the reference by design
 # (fast_layered.cuh) and is built with FMA contraction and the approximate division / sqrt / exp / sin / cos.
 PER_FILE_FLAGS = {"wavefront.cu": ["-fmad=false"], "bsdf_hooks.cu": ["-fmad=false"],
-                  "shade_layered.cu": ["--use_fast_math"]}
+                  "shade_layered.cu": ["--use_fast_math"], "wavefront_relaxed.cu": ["--use_fast_math"]}
 
 
 def _sources() -> list[Path]:

@@ -98,7 +98,7 @@ int b2pt_create(const B2ptSceneDesc* scene, const B2ptConfig* cfg, B2ptRenderer*
         B2PT_CUDA(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
         B2PT_CUDA(cudaEventCreate(&r->ev0));
         B2PT_CUDA(cudaEventCreate(&r->ev1));
-        build_scene(*scene, r->scene, r->stream);
+        build_scene(*scene, r->scene, r->stream, r->cfg.bvh_leaf_size);
         r->d_counters.alloc(1);
         r->d_counters.zero(r->stream);
         B2PT_CUDA(cudaStreamSynchronize(r->stream));

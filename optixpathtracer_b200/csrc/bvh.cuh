@@ -44,11 +44,16 @@ static_assert(sizeof(BvhNode2) == 64, "node must be 64 bytes");
 // lo = hi = +inf (never hit) and child = kEmptyChild.
 struct alignas(16) BvhNode4 {
     float4 lox, hix, loy, hiy, loz, hiz;   // component k = slot k
-    int32_t child[4];                      // >= 0: binary node index (= BvhNode4 index); < 0: ~(triangle slot)
+    int32_t child[4];                      // >= 0: wide node index; < 0: leaf, ~(first triangle slot | (count - 1) << 28)
     int32_t pad[4];
 };
 static_assert(sizeof(BvhNode4) == 128, "wide node must be 128 bytes");
 constexpr int32_t kEmptyChild = 0x7ffffffe;
+// A leaf child of a wide node names a RUN of triangle records: ~(first | (count - 1) << kLeafCountShift), count <= 8.
+// One triangle per leaf (the default) is count = 1: ~slot, as in the binary nodes.
+constexpr int kLeafCountShift = 28;
+constexpr int kDefaultLeafSize = 2;   // 1 | 2 | 3 | 4 measured: profiles/r02_ab_leaf_size.txt
+constexpr uint32_t kLeafSlotMask = (1u << kLeafCountShift) - 1u;
 
 // Traversal stacks (per ray): the binary kernels push one entry per level below the root plus a sentinel, the wide
 // kernels at most three per level plus the sentinel.  A Karras tree over 63-bit Morton keys with index tie-breaks

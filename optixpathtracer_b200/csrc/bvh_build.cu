@@ -297,6 +297,13 @@ static int collapse_greedy() {
     return v;
 }
 
+// triangles per leaf of the wide tree: B2ptConfig::bvh_leaf_size, 0 = default; B2PT_LEAF overrides (A/B)
+static int wide_leaf_size(int cfg_leaf_size) {
+    static const int env = [] { const char* e = getenv("B2PT_LEAF"); return e ? atoi(e) : 0; }();
+    const int v = env > 0 ? env : (cfg_leaf_size > 0 ? cfg_leaf_size : kDefaultLeafSize);
+    return v < 1 ? 1 : (v > 8 ? 8 : v);
+}
+
 // ---- K3d: collapse binary nodes into 4-wide nodes ---------------------------------------
 // Wide node i describes the subtree of binary node i.  Its slots start as the two children of i; while
 // a slot is free, the internal slot with the largest surface area is replaced by its own two children
@@ -357,8 +364,24 @@ __device__ __forceinline__ BvhNode4P pack4(const Slot4 sl[4]) {
     return p;
 }
 
+// Multi-triangle leaves (B2ptConfig::bvh_leaf_size = L > 1): a slot whose binary subtree holds at most L triangles
+// becomes ONE leaf that names the run of triangle records — a Karras subtree covers a contiguous range of the
+// Morton-sorted triangles, and the records are stored in that order — child = ~(first | (count - 1) << 28)
+// (kLeafCountShift, bvh.cuh; count <= 8, first < 2^28).  A ray that enters the slot's box tests the whole run
+// instead of visiting one more node.  The size of a subtree is found by walking to its leftmost and rightmost
+// leaf, at most L - 1 levels each way.
+__device__ __forceinline__ void leafify(Slot4& b, const BvhNode2* __restrict__ nodes, int leaf_size) {
+    if (leaf_size <= 1 || b.child < 0) return;
+    int lo = b.child, hi = b.child;
+    for (int s = 0; s < leaf_size && lo >= 0; s++) lo = nodes[lo].child0;
+    for (int s = 0; s < leaf_size && hi >= 0; s++) hi = nodes[hi].child1;
+    if (lo >= 0 || hi >= 0) return;
+    const int first = ~lo, count = ~hi - first + 1;
+    if (count <= leaf_size && first < (1 << kLeafCountShift)) b.child = ~(first | ((count - 1) << kLeafCountShift));
+}
+
 __global__ void __launch_bounds__(kThreads)
-k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restrict__ wide, int greedy) {
+k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restrict__ wide, int greedy, int leaf_size) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_nodes) return;
     const BvhNode2 nd = nodes[i];
@@ -366,7 +389,8 @@ k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restric
     int k = 0;
 #pragma unroll
     for (int s = 0; s < 2; s++) {
-        const Slot4 b = slot_of(nd, s);
+        Slot4 b = slot_of(nd, s);
+        leafify(b, nodes, leaf_size);
         if (b.lx <= b.hx) sl[k++] = b;             // drops the never-hit slot of a one-triangle scene
     }
     if (greedy) {
@@ -381,7 +405,10 @@ k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restric
             if (pick < 0) break;
             const BvhNode2 g = nodes[sl[pick].child];
             sl[pick] = slot_of(g, 0);
-            sl[k++] = slot_of(g, 1);
+            sl[k] = slot_of(g, 1);
+            leafify(sl[pick], nodes, leaf_size);
+            leafify(sl[k], nodes, leaf_size);
+            k++;
         }
     } else {
         const int k0 = k;
@@ -389,7 +416,10 @@ k_collapse4(int n_nodes, const BvhNode2* __restrict__ nodes, BvhNode4* __restric
             if (sl[j].child < 0) continue;
             const BvhNode2 g = nodes[sl[j].child];
             sl[j] = slot_of(g, 0);
-            sl[k++] = slot_of(g, 1);
+            sl[k] = slot_of(g, 1);
+            leafify(sl[j], nodes, leaf_size);
+            leafify(sl[k], nodes, leaf_size);
+            k++;
         }
     }
     // empty slot: lo = hi = +inf fails the slab test for every direction (an INVERTED box would pass it:
@@ -624,7 +654,7 @@ static void create_textures(const B2ptSceneDesc& desc, SceneBuffers& out, cudaSt
     out.textures.upload(out.texture_objects.data(), out.texture_objects.size(), stream);
 }
 
-void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stream) {
+void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stream, int leaf_size) {
     B2PT_REQUIRE(desc.n_meshes >= 0 && (desc.n_meshes == 0 || desc.meshes), B2PT_E_INVALID, "bad mesh array");
     B2PT_REQUIRE(desc.n_textures >= 0 && (desc.n_textures == 0 || desc.textures), B2PT_E_INVALID,
                  "bad texture array");
@@ -800,7 +830,7 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
         d_front[0].alloc((size_t)nn); d_front[1].alloc((size_t)nn);
         d_remap.alloc((size_t)nn);
         d_counts.alloc(2 * (kMaxLevels + 1));
-        k_collapse4<<<blocks_for(nn), kThreads, 0, stream>>>(nn, out.nodes.get(), d_wide.get(), collapse_greedy());
+        k_collapse4<<<blocks_for(nn), kThreads, 0, stream>>>(nn, out.nodes.get(), d_wide.get(), collapse_greedy(), wide_leaf_size(leaf_size));
         B2PT_CUDA(cudaMemsetAsync(d_level.get(), 0xff, (size_t)nn * 4, stream));
         d_counts.zero(stream);
         uint32_t* cw = d_counts.get();                     // per-level node counts of the wide tree ...

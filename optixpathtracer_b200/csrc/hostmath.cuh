@@ -109,10 +109,19 @@ B2PT_HD float sincosf_host(float y) {
     return COS ? ::cosf(y) : ::sinf(y);   // outside the path's range: the platform's function
 }
 
+#if defined(B2PT_RELAXED_MATH) && defined(__CUDA_ARCH__)
+// wavefront_relaxed.cu (the A/B build of the Philox kernels, B2PT_RELAXED=1): the hardware approximations, evaluated
+// in [-pi, pi) where sin.approx / cos.approx are accurate (the path passes angles in [0, 2 pi])
+B2PT_HD float sinf_host(float y) { return -__sinf(y - 3.14159265358979323846f); }
+B2PT_HD float cosf_host(float y) { return -__cosf(y - 3.14159265358979323846f); }
+B2PT_HD float expf_host(float x) { return __expf(x); }
+B2PT_HD float expf_host_exact(float x) {
+#else
 B2PT_HD float sinf_host(float y) { return sincosf_host<false>(y); }
 B2PT_HD float cosf_host(float y) { return sincosf_host<true>(y); }
 
 B2PT_HD float expf_host(float x) {
+#endif
     // 2^(i/32) with i subtracted from the exponent field (i << 47), so that adding k << 47 for
     // k = 32 e + i lands on 2^e * 2^(i/32)
     const uint64_t tab[32] = {

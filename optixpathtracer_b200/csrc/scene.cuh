@@ -88,7 +88,8 @@ struct SceneBuffers {
 int trace_wide_formats();
 bool trace_uses_wide(int any_alpha_texture);
 
-// Upload + flatten + LBVH build (K1-K3) on `stream`.  Throws b2pt::Error.
-void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stream);
+// Upload + flatten + LBVH build (K1-K3) on `stream`.  Throws b2pt::Error.  leaf_size = B2ptConfig::bvh_leaf_size:
+// triangles per leaf of the wide tree (0 = the default, 1..8; bvh_build.cu `leafify`).
+void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stream, int leaf_size = 0);
 
 }  // namespace b2pt

@@ -77,23 +77,28 @@ k_layered_prep(WaveParams wp, PathState st, SurfaceState sf, LayeredScratch ls, 
         float alpha = 0.0f;
         if (q < n) {
             i = lq[q];
+            // every load of the hit before the first store: the kernel is bound by memory latency, and a load
+            // that follows a store through a pointer the compiler cannot tell apart waits for it
             const float3 ns = v3(sf.nx[i], sf.ny[i], sf.nz[i]);
+            const float3 rd = v3(st.dx[i], st.dy[i], st.dz[i]);
+            const float rough = sf.rough[i];
+            const uint32_t id = st.id[i];
+            const float3 albedo = v3(sf.ar[i], sf.ag[i], sf.ab[i]);
+            const uint32_t info = sf.info[i];
+            const float3 p = v3(sf.px[i], sf.py[i], sf.pz[i]);
             float3 t, b;
             tangent_frame(ns, t, b);
-            wo = to_local(t, b, ns, normalize(-v3(st.dx[i], st.dy[i], st.dz[i])));
-            const float rough = sf.rough[i];
+            wo = to_local(t, b, ns, normalize(-rd));
             alpha = rough * rough;                       // Surface.h:26
-            const fastlayer::WalkKey key = task_key(wp, st.id[i], bounce, 0u);
-            ls.task[i].q[0] = make_float4(wo.x, wo.y, wo.z, alpha);
-            ls.task[i].q[1] = make_float4(sf.ar[i], sf.ag[i], sf.ab[i], __uint_as_float(key.k0));
-            ls.task[i].q[3] = make_float4(__uint_as_float(key.k1), 0.0f, 0.0f, 0.0f);
-            const uint32_t info = sf.info[i];
+            const fastlayer::WalkKey key = task_key(wp, id, bounce, 0u);
             if ((info & kInfoHasLight) && (info & kInfoVisible)) {
                 const B2ptPointLight& L = wp.lights[info & 0xffu];
-                const float3 p = v3(sf.px[i], sf.py[i], sf.pz[i]);
                 wl = to_local(t, b, ns, normalize(v3(L.position[0], L.position[1], L.position[2]) - p));
                 want_f = wo.z * wl.z > 0.0f;
             }
+            ls.task[i].q[0] = make_float4(wo.x, wo.y, wo.z, alpha);
+            ls.task[i].q[1] = make_float4(albedo.x, albedo.y, albedo.z, __uint_as_float(key.k0));
+            ls.task[i].q[3] = make_float4(__uint_as_float(key.k1), 0.0f, 0.0f, 0.0f);
         }
         const uint32_t j = warp_append(want_f, lcounts);
         if (want_f) {
@@ -198,26 +203,34 @@ k_layered_finish(WaveParams wp, PathState st, PathState nx, SurfaceState sf, Lay
         uint32_t id = 0;
         if (q < n) {
             const uint32_t i = lq[q];
+            // all loads by slot first, then the partial sums by f-list position: two dependent rounds of memory
+            // latency per hit instead of six (the conditions that used to guard the loads guard only the math now)
             id = st.id[i];
             beta = v3(st.bx[i], st.by[i], st.bz[i]);
             radiance = v3(st.rx[i], st.ry[i], st.rz[i]);
             const float3 p = v3(sf.px[i], sf.py[i], sf.pz[i]);
             const uint32_t j = ls.fidx[i];
-            if (j != kNoF) {   // NEE (devicePrograms.cu:453-472) with f = entrance reflection + mean of the five walks
-                const float4 q0 = ls.task[i].q[0], q2 = ls.task[i].q[2];
+            const float4 q0 = ls.task[i].q[0], q2 = ls.task[i].q[2];
+            const uint32_t info = sf.info[i];
+            const float3 wi = v3(ls.swx[i], ls.swy[i], ls.swz[i]);
+            const float3 sb = v3(ls.sbx[i], ls.sby[i], ls.sbz[i]);
+            const float3 ns = v3(sf.nx[i], sf.ny[i], sf.nz[i]);
+            const float3 ng = v3(sf.gx[i], sf.gy[i], sf.gz[i]);
+            const bool has_f = j != kNoF;
+            const uint32_t jj = has_f ? j : 0u;      // a hit without f walks reads position 0 and ignores it
+            float3 sum = v3(0.0f);
+#pragma unroll
+            for (int w = 0; w < fastlayer::kWalks; w++) {
+                const float* fp = ls.fpart + (size_t)w * 3u * ls.capacity + jj;
+                sum += v3(fp[0], fp[ls.capacity], fp[2 * (size_t)ls.capacity]);
+            }
+            if (has_f) {   // NEE (devicePrograms.cu:453-472) with f = entrance reflection + mean of the five walks
                 float3 wo = v3(q0.x, q0.y, q0.z), wl = v3(q2.x, q2.y, q2.z);
                 const float cos_l = fabsf(wl.z);
                 if (wo.z < 0.0f) { wo = -wo; wl = -wl; }
-                float3 sum = v3(0.0f);
-#pragma unroll
-                for (int w = 0; w < fastlayer::kWalks; w++) {
-                    const float* fp = ls.fpart + (size_t)w * 3u * ls.capacity + j;
-                    sum += v3(fp[0], fp[ls.capacity], fp[2 * (size_t)ls.capacity]);
-                }
                 const float3 f = v3(fastlayer::entrance_reflection(wo, wl, q0.w)) + sum * (1.0f / (float)fastlayer::kWalks);
                 const float3 spectrum = f * cos_l;
                 if (nonzero(spectrum)) {
-                    const uint32_t info = sf.info[i];
                     const B2ptPointLight& L = wp.lights[info & 0xffu];
                     const float p_light = wp.n_lights == 1 ? 1.0f : 1.0f / (float)wp.n_lights;
                     const float3 dl = p - v3(L.position[0], L.position[1], L.position[2]);
@@ -225,13 +238,11 @@ k_layered_finish(WaveParams wp, PathState st, PathState nx, SurfaceState sf, Lay
                     radiance += (beta * spectrum * li) / p_light;
                 }
             }
-            const float3 wi = v3(ls.swx[i], ls.swy[i], ls.swz[i]);
             if (wi.z != 0.0f) {   // GetNewRayDirection + throughput + next ray (:474-509)
-                beta *= v3(ls.sbx[i], ls.sby[i], ls.sbz[i]);
-                const float3 ns = v3(sf.nx[i], sf.ny[i], sf.nz[i]);
+                beta *= sb;
                 float3 t, b;
                 tangent_frame(ns, t, b);
-                float3 offset = 1e-3f * v3(sf.gx[i], sf.gy[i], sf.gz[i]);
+                float3 offset = 1e-3f * ng;
                 if (wi.z < 0.0f) offset = -offset;
                 next_o = p + offset;
                 next_d = normalize(to_world(t, b, ns, wi));

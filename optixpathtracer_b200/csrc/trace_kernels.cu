@@ -94,14 +94,38 @@ struct AnyIo {
     ShadowRays sh;
     uint32_t* info;
     uint8_t* occluded;
-    __device__ __forceinline__ bool load(uint32_t i, float3& o, float3& d, float& tmax_out) const {
+    // position in the light-ordered work list -> slot (ShadowRays::order).  The bucket sizes are re-read from
+    // memory (L1) at each use — a few times per ray — instead of living in registers through the traversal loop.
+    __device__ __forceinline__ uint32_t slot_of(uint32_t q) const {
+        if (!sh.order) return q;
+        uint32_t k = 0, base = 0;
+#pragma unroll
+        for (int b = 0; b < kShadowBuckets - 1; b++) {
+            const uint32_t nb = __ldg(sh.bucket_n + b);
+            if (q >= base + nb && k == (uint32_t)b) {
+                base += nb;
+                k = (uint32_t)b + 1u;
+            }
+        }
+        return sh.order[(size_t)k * sh.capacity + (q - base)];
+    }
+    __device__ __forceinline__ uint32_t count(uint32_t n_slots) const {
+        if (!sh.order) return n_slots;
+        uint32_t n = 0;
+#pragma unroll
+        for (int b = 0; b < kShadowBuckets; b++) n += __ldg(sh.bucket_n + b);
+        return n;
+    }
+    __device__ __forceinline__ bool load(uint32_t q, float3& o, float3& d, float& tmax_out) const {
+        const uint32_t i = slot_of(q);
         tmax_out = sh.tmax[i];
         if (!(tmax_out >= 0.0f)) return false;   // no shadow ray for this slot
         o = v3(sh.ox[i], sh.oy[i], sh.oz[i]);
         d = v3(sh.dx[i], sh.dy[i], sh.dz[i]);
         return true;
     }
-    __device__ __forceinline__ void store(uint32_t i, const HitRecord&, bool occ) const {
+    __device__ __forceinline__ void store(uint32_t q, const HitRecord&, bool occ) const {
+        const uint32_t i = slot_of(q);
         if (info && !occ) info[i] |= kInfoVisible;
         if (occluded) occluded[i] = occ ? 1 : 0;
     }
@@ -154,11 +178,12 @@ k_any_w(DeviceScene sc, ShadowRays sh, const uint32_t* __restrict__ n_active, fl
     TraceStats ts = {0, 0, 0, 0, 0};
     const AnyIo io{sh, info, occluded};
     const void* nodes = STEP == 6 ? (const void*)sc.nodes4p : (const void*)sc.nodes4;
+    const uint32_t n_rays = io.count(*n_active);   // the light-ordered list holds only the slots with a ray
     if constexpr (ALPHA)
-        trace_wide<true, STATS, STEP, SS>(nodes, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io,
+        trace_wide<true, STATS, STEP, SS>(nodes, sc.tris, sc.n_nodes, sc.max_abs, n_rays, tmin, io,
                                           AlphaCutout<DeviceTexFetch>{sc, DeviceTexFetch{sc.textures}}, ts, pol);
     else
-        trace_wide<true, STATS, STEP, SS>(nodes, sc.tris, sc.n_nodes, sc.max_abs, *n_active, tmin, io, AcceptAllHits(), ts, pol);
+        trace_wide<true, STATS, STEP, SS>(nodes, sc.tris, sc.n_nodes, sc.max_abs, n_rays, tmin, io, AcceptAllHits(), ts, pol);
     if (STATS) {
         atomicAdd(&counters->nodes_any, (unsigned long long)ts.nodes);
         atomicAdd(&counters->tris_any, (unsigned long long)ts.tris);
@@ -355,15 +380,17 @@ void launch_closest(const LaunchCfg& lc, const DeviceScene& sc, const PathState&
     if (lc.launch_counter) ++*lc.launch_counter;
 }
 
-void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh,
+void launch_any(const LaunchCfg& lc, const DeviceScene& sc, const ShadowRays& sh_in,
                 const uint32_t* n_active, float tmin, uint32_t* info, uint8_t* occluded,
                 TraceCounters* counters) {
     const bool alpha = sc.any_alpha_texture != 0;
+    ShadowRays sh = sh_in;
     if (use_persistent() && use_wide()) {
         B2PT_WIDE_LAUNCH(k_any_w, B2PT_WIDE_ARGS_A);
         if (lc.launch_counter) ++*lc.launch_counter;
         return;
     }
+    sh.order = nullptr;   // the A/B fallback kernels scan the slots (tmax < 0 marks the empty ones)
     if (use_persistent()) {
         if (lc.stats && alpha)
             k_any_p<true, true><<<lc.grid, kTraceThreads, 0, lc.stream>>>(sc, sh, n_active, tmin, info, occluded, counters, warp_policy());

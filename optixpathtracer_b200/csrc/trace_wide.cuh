@@ -200,8 +200,11 @@ __device__ __forceinline__ void trace_wide(const void* __restrict__ nodes_v, con
             }
             const uint32_t tris_before = ts.tris;
             while (pend < 0) {
-                const int slot = ~pend;
-                pend = 0;
+                // a leaf names a run of triangle records (bvh.cuh: first | (count - 1) << 28); the run is walked one
+                // record per trip, the rest of it stays parked in `pend`
+                const uint32_t leaf = ~(uint32_t)pend;
+                const int slot = (int)(leaf & kLeafSlotMask);
+                pend = leaf > kLeafSlotMask ? (int)~(leaf + 1u - (1u << kLeafCountShift)) : 0;
                 if (STATS) ts.tris++;
                 // (reading the 48-byte record as one 256-bit + one 128-bit load, chosen by the slot's parity, was
                 // measured 1-2 % slower than these three loads: profiles/r01_ab_node_step.txt)
@@ -231,6 +234,7 @@ __device__ __forceinline__ void trace_wide(const void* __restrict__ nodes_v, con
                             if constexpr (ANY) {
                                 occluded = true;
                                 node = kStackSentinel;
+                                pend = 0;
                                 break;
                             } else {
                                 c = resolve_in_fp64(tris, r.o, r.d, tmin, tmax_f, slot, c);
@@ -251,6 +255,7 @@ __device__ __forceinline__ void trace_wide(const void* __restrict__ nodes_v, con
                     if (occ) {
                         occluded = true;
                         node = kStackSentinel;
+                        pend = 0;
                         break;
                     }
                 } else {
@@ -265,7 +270,7 @@ __device__ __forceinline__ void trace_wide(const void* __restrict__ nodes_v, con
                         c = resolve_in_fp64(tris, r.o, r.d, tmin, tmax_f, slot, c);
                     }
                 }
-                if (node < 0) {
+                if (pend == 0 && node < 0) {
                     pend = node;
                     node = B2PT_POP();
                 }

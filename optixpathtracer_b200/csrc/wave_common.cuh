@@ -40,7 +40,8 @@ constexpr int kCountsActive = 0;          // [100]
 constexpr int kCountsQueued = 100;        // [100][4]
 constexpr int kCountsPartition = 501;     // [100][4][2] K7p cursors (LCG modes)
 constexpr int kCountsLayered = 1301;      // [100][4]: f-hit count, task cursor, spare, spare (Philox engine)
-constexpr int kCountsWords = 1301 + 400;
+constexpr int kCountsShadow = 1701;        // [100][4]: shadow rays per light bucket (K6 -> K8, ShadowRays::bucket_n)
+constexpr int kCountsWords = 1701 + 400;
 
 // ---- the layered walk engine (shade_layered.cu) ----------------------------------------------------
 // B2PT_LAYERED_ENGINE=0 sends the Philox mode through the serial k_shade<LAYERED> too (A/B, tests)

@@ -29,7 +29,16 @@
 #include "traverse.cuh"
 #include "wave_common.cuh"
 
+// This file is compiled twice.  As wavefront.cu (-fmad=false, host-library sin / cos / exp: the arithmetic that
+// reproduces the reference bit for bit) it holds the kernels of all three generators and the scheduler.  Through
+// wavefront_relaxed.cu (B2PT_RELAXED_MATH, --use_fast_math) it holds only the PHILOX kernels, in relaxed arithmetic —
+// what the production generator runs (B2PT_RELAXED=0 switches back): its images are an independent estimate of the
+// reference's anyway, so the bit-parity arithmetic only cost it instructions.
 namespace b2pt {
+
+#if !defined(B2PT_RELAXED_MATH)
+void enqueue_wave_philox_relaxed(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwrite);
+#endif
 
 namespace {
 
@@ -68,9 +77,14 @@ k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restri
     const uint32_t iters = (n + stride - 1) / stride;
     const DeviceTexFetch tex{sc.textures};
     uint32_t* qn = wc.queued + 4 * bounce;
+    // block-aggregated append to the light buckets; two copies, used by alternate trips of the loop
+    __shared__ uint32_t s_cnt[2][kThreads / 32][kShadowBuckets];
+    __shared__ uint32_t s_base[2][kShadowBuckets];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     for (uint32_t it = 0; it < iters; it++) {
         const uint32_t i = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
         int kind = -1;
+        int bucket = -1;   // light bucket of this slot's shadow ray, -1: none
         bool culled = false;
         if (i < n) {
             HitRecord hit;
@@ -135,6 +149,35 @@ k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restri
                 sh.ox[i] = s.sh_o.x; sh.oy[i] = s.sh_o.y; sh.oz[i] = s.sh_o.z;
                 sh.dx[i] = s.sh_d.x; sh.dy[i] = s.sh_d.y; sh.dz[i] = s.sh_d.z;
                 sh.tmax[i] = trace_shadow ? s.sh_tmax : -1.0f;
+                if (trace_shadow) bucket = s.light & (kShadowBuckets - 1);
+            }
+        }
+        if (sh.order) {
+            // K8's work list, ordered by light (ShadowRays, wavefront.cuh).  The append is aggregated over the BLOCK:
+            // the rays that the block's 128 consecutive slots send to one light land next to each other in that
+            // light's bucket — a warp of K8 then traces rays from neighbouring paths to the same light — and the
+            // four bucket counters see one atomic per block and trip instead of one per warp (per-warp appends made
+            // K6 twice as slow and left K8's warps as mixed as before: profiles/r02_ab_sort_shadow.txt).
+            uint32_t* cnt = s_cnt[it & 1u][0];
+            uint32_t mine = 0;
+#pragma unroll
+            for (int k = 0; k < kShadowBuckets; k++) {
+                const uint32_t m = __ballot_sync(0xffffffffu, bucket == k);
+                if (lane == 0) cnt[warp * kShadowBuckets + k] = (uint32_t)__popc(m);
+                if (bucket == k) mine = (uint32_t)__popc(m & ((1u << lane) - 1u));
+            }
+            __syncthreads();
+            if (threadIdx.x < kShadowBuckets) {
+                uint32_t tot = 0;
+#pragma unroll
+                for (int w = 0; w < kThreads / 32; w++) tot += cnt[w * kShadowBuckets + threadIdx.x];
+                s_base[it & 1u][threadIdx.x] = tot ? atomicAdd(sh.bucket_n + threadIdx.x, tot) : 0u;
+            }
+            __syncthreads();
+            if (bucket >= 0) {
+                uint32_t pos = s_base[it & 1u][bucket] + mine;
+                for (uint32_t w = 0; w < warp; w++) pos += cnt[w * kShadowBuckets + bucket];
+                sh.order[(size_t)bucket * sh.capacity + pos] = i;
             }
         }
 #pragma unroll
@@ -383,17 +426,27 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
     // the layered BSDF with the production generator runs as a walk engine (shade_layered.cu); the LCG modes — whose
     // draws must come in the reference's order — run the serial kernel below, visible hits first (K7p)
     const bool engine = std::is_same<Rng, PhiloxRng>::value && kinds[3] && layered_engine_enabled();
+    // A/B, off by default: c2 +1.9 %, c5 +1.9 %, c4 -0.6 % (profiles/r02_ab_sort_shadow.txt)
+    static const bool sort_shadow = [] { const char* e = getenv("B2PT_SORT_SHADOW"); return e && atoi(e) != 0; }();
     for (int b = 0; b < wp.max_bounces; b++) {
         const PathState& cur = r->st[b & 1];
         const PathState& nxt = r->st[(b + 1) & 1];
         launch_closest(lc, sc, cur, wc.active + b, 0.0f, 100.0f, r->d_hits.get(), r->d_counters.get(), /*finish=*/false);   // tmin 0, tmax 100 (:652)
         mark(kClsClosest);
-        k_surface<Rng><<<grid, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, r->shadow, r->d_queues.get(),
+        // B2PT_SORT_SHADOW=1: K8 takes its rays from a light-ordered list instead of scanning the slots.  The list lives in d_queues2,
+        // which the serial layered kernel's partition pass (K7p) only overwrites after K8 has read it.
+        ShadowRays shadow = r->shadow;
+        if (sort_shadow && wp.n_lights > 0) {
+            shadow.order = r->d_queues2.get();
+            shadow.bucket_n = r->d_counts.get() + kCountsShadow + kShadowBuckets * b;
+            shadow.capacity = wp.capacity;
+        }
+        k_surface<Rng><<<grid, kThreads, 0, s>>>(wp, sc, cur, r->d_hits.get(), r->surf, shadow, r->d_queues.get(),
                                                  wc, (uint32_t)b, r->d_wave_out.get(), r->d_counters.get());
         count();
         mark(kClsSurface);
         if (wp.n_lights > 0) {
-            launch_any(lc, sc, r->shadow, wc.active + b, 0.0f, r->surf.info, nullptr, r->d_counters.get());
+            launch_any(lc, sc, shadow, wc.active + b, 0.0f, r->surf.info, nullptr, r->d_counters.get());
             mark(kClsAny);
         }
         const uint32_t* q = r->d_queues.get();
@@ -436,6 +489,11 @@ void enqueue_wave(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwr
 
 }  // namespace
 
+#if defined(B2PT_RELAXED_MATH)
+void enqueue_wave_philox_relaxed(B2ptRenderer* r, const WaveParams& wp, float* dst, bool overwrite) {
+    enqueue_wave<PhiloxRng>(r, wp, dst, overwrite);
+}
+#else
 void render_frames(B2ptRenderer* r, int spp, bool accumulate) {
     B2PT_REQUIRE(r->width > 0 && r->height > 0, B2PT_E_STATE, "resize first");
     B2PT_REQUIRE(r->have_camera, B2PT_E_STATE, "set_camera first");
@@ -479,6 +537,9 @@ void render_frames(B2ptRenderer* r, int spp, bool accumulate) {
     wp.seed = r->cfg.seed;
     wp.capacity = capacity;
     static const int cull_nee = [] { const char* e = getenv("B2PT_CULL_NEE"); return e ? atoi(e) : 1; }();
+    // the Philox kernels in relaxed arithmetic (wavefront_relaxed.cu) unless B2PT_RELAXED=0: c2 +10 %, c3 +9 %, c5 +2 %
+    // (the light shade kernels run twice as fast; profiles/r02_ab_relaxed.txt), gated by tests/test_relaxed_gpu.py
+    static const bool relaxed = [] { const char* e = getenv("B2PT_RELAXED"); return !e || atoi(e) != 0; }();
     wp.cull_nee = cull_nee;
     wp.cull_layered = cull_nee && r->cfg.rng_mode == B2PT_RNG_PHILOX && layered_engine_enabled();
     float* dst = accumulate ? r->d_accum.get() : r->d_frame.get();
@@ -497,7 +558,10 @@ void render_frames(B2ptRenderer* r, int spp, bool accumulate) {
             switch (r->cfg.rng_mode) {
                 case B2PT_RNG_LCG_DEVICE: enqueue_wave<LcgRng<false>>(r, wp, dst, !accumulate); break;
                 case B2PT_RNG_LCG_HOST: enqueue_wave<LcgRng<true>>(r, wp, dst, !accumulate); break;
-                default: enqueue_wave<PhiloxRng>(r, wp, dst, !accumulate); break;
+                default:
+                    if (relaxed) enqueue_wave_philox_relaxed(r, wp, dst, !accumulate);
+                    else enqueue_wave<PhiloxRng>(r, wp, dst, !accumulate);
+                    break;
             }
         }
     }
@@ -525,5 +589,6 @@ void resolve_mean(B2ptRenderer* r) {
     r->kernel_launches++;
     B2PT_CUDA(cudaGetLastError());
 }
+#endif  // !B2PT_RELAXED_MATH
 
 }  // namespace b2pt

@@ -50,7 +50,16 @@ constexpr uint32_t kInfoVisible = 1u << 10;
 struct ShadowRays {
     float *ox, *oy, *oz, *dx, *dy, *dz;
     float* tmax;              // < 0: no shadow ray for this slot
+    // Light-ordered work list (optional, the renderer's K6 fills it; the parity hooks leave it null): the slots
+    // that DO hold a shadow ray, appended to bucket (light index & 3), so that the rays a warp of K8 traces
+    // together aim at the same light and the empty slots are never visited.  order[k * capacity + j] = slot of
+    // the j-th ray of bucket k, bucket_n[k] = rays in bucket k.  The answer of a ray does not depend on where it
+    // sits in the list (K8 writes by slot).
+    uint32_t* order = nullptr;      // [kShadowBuckets][capacity]
+    uint32_t* bucket_n = nullptr;   // [kShadowBuckets], zeroed with the wave's counters
+    uint32_t capacity = 0;
 };
+constexpr int kShadowBuckets = 4;
 constexpr int kShadowWords = 7;
 
 struct TraceCounters {

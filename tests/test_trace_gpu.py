@@ -133,6 +133,36 @@ def test_rays_through_mesh_vertices_and_edges(oracle):
         assert np.array_equal(r.TraceAny(o, d, tm), oracle.any(soup, o, d, tm))
 
 
+@pytest.mark.parametrize("leaf", [1, 2, 3, 5, 8])
+def test_multi_triangle_leaves(oracle, leaf):
+    """B2ptConfig::bvh_leaf_size: a leaf of the wide tree names a run of up to `leaf` triangle records.  Same hits,
+    same bits, whatever the run length — on a closed mesh with coincident shells (several triangles of one run hit at
+    the same distance) and on random soup; fewer wide nodes the longer the runs."""
+    if os.environ.get("B2PT_LEAF"):
+        pytest.skip("B2PT_LEAF overrides the config field")
+    from optixpathtracer_b200 import scenes as S
+    pos, _, _, idx = S.uv_sphere(20, 10)
+    tri = pos[idx].astype(f32)
+    rng = np.random.default_rng(77)
+    soup = np.concatenate([tri, tri, tri[::-1] * f32(1.7), rng.uniform(-2, 2, (300, 3, 3)).astype(f32)]).astype(f32)
+    o, d = random_rays(rng, 5000, [-3, -3, -3], [3, 3, 3])
+    verts = pos.astype(np.float64)
+    org = rng.normal(size=verts.shape)
+    org = 4.0 * org / np.linalg.norm(org, axis=1, keepdims=True)
+    dv = verts - org
+    dv /= np.linalg.norm(dv, axis=1, keepdims=True)
+    o = np.concatenate([o, org.astype(f32)])
+    d = np.concatenate([d, dv.astype(f32)])
+    with _renderer(_soup_scene(soup), bvh_leaf_size=leaf) as r:
+        _compare(r, oracle, soup, o, d)
+        _compare(r, oracle, soup, o, d, tmin=0.8, tmax=4.1)
+        tm = np.full(len(o), 3.9, f32)
+        assert np.array_equal(r.TraceAny(o, d, tm), oracle.any(soup, o, d, tm))
+        n_wide = r.Stats()["n_wide_nodes"]
+    with _renderer(_soup_scene(soup), bvh_leaf_size=1) as r1:
+        assert n_wide <= r1.Stats()["n_wide_nodes"] and (leaf == 1 or n_wide < r1.Stats()["n_wide_nodes"])
+
+
 def test_far_origins_small_triangles(oracle):
     rng = np.random.default_rng(11)
     c = rng.uniform(-1, 1, (4000, 1, 3))
