@@ -17,12 +17,12 @@ run() {  # config scaling n
   python -c "
 import json; d=json.load(open('$out')); print('$c $sc n=$n', round(d['value'],1), 'Msamples/s e2e', round(d['e2e']['value'],1), 'ms/step', round(d['ms_per_step'],2), d['config']['spp_per_step_per_gpu'], 'spp/gpu/step')" 2>/dev/null || tail -3 ${out%.json}.err
 }
-for n in 1 2 4 8; do
+for n in ${NS:-2 4 8}; do
   [ $n -le $NG ] || continue
   run c5 strong $n
   run c1 strong $n
 done
-for n in 2 4 8; do
+for n in ${NS:-2 4 8}; do
   [ $n -le $NG ] || continue
   run c4 weak $n
 done
