@@ -24,6 +24,13 @@ namespace b2pt {
 
 namespace {
 
+// B2PT_WARP_APPEND (build-time A/B): one atomic per warp instead of one per block
+#if defined(B2PT_WARP_APPEND)
+#define B2PT_APPEND(want, counter) warp_append(want, counter)
+#else
+#define B2PT_APPEND(want, counter) block_append(want, counter, s_app, it)
+#endif
+
 constexpr uint32_t kNoF = 0xffffffffu;
 // K7d-p / K7d-f are gather / scatter kernels bound by memory latency (ncu: 12-16 % of the issue slots used), but more
 // resident threads do not help them: built for 16 blocks per SM (32 registers, 28-40 bytes of spills) they were 10-30 %
@@ -68,6 +75,7 @@ k_layered_prep(WaveParams wp, PathState st, SurfaceState sf, LayeredScratch ls, 
     const uint32_t n = queued[4 * bounce + kBsdfLayered];
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t iters = (n + stride - 1) / stride;
+    __shared__ BlockAppendScratch s_app;
     for (uint32_t it = 0; it < iters; it++) {
         const uint32_t q = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
         bool want_f = false;
@@ -100,7 +108,7 @@ k_layered_prep(WaveParams wp, PathState st, SurfaceState sf, LayeredScratch ls, 
             ls.task[i].q[1] = make_float4(albedo.x, albedo.y, albedo.z, __uint_as_float(key.k0));
             ls.task[i].q[3] = make_float4(__uint_as_float(key.k1), 0.0f, 0.0f, 0.0f);
         }
-        const uint32_t j = warp_append(want_f, lcounts);
+        const uint32_t j = B2PT_APPEND(want_f, lcounts);
         if (want_f) {
             ls.flist[j] = i;
             ls.task[i].q[2] = make_float4(wl.x, wl.y, wl.z, fastlayer::walk_lambda_wi(wo.z < 0.0f ? -wl : wl, alpha));
@@ -129,6 +137,9 @@ k_layered_engine(LayeredScratch ls, const uint32_t* __restrict__ lq, const uint3
     WalkKey key = {0u, 0u, 0u, 0u};
     uint32_t out = 0;            // f walk: f-list position; sample walk: slot
     bool exhausted = false;      // warp-uniform
+    // (one atomic on the task cursor per fetch; reserving 128 tasks per atomic and handing them out over the next
+    // fetches was measured slower — engine 93.9 -> 98.5 ms per c4 step, profiles/r02_ab_atomics.txt — the cursor is
+    // not what the engine waits for)
     for (;;) {
         const uint32_t idle = __ballot_sync(0xffffffffu, k.step < 0);
         if (!exhausted && __popc(idle) >= REFILL) {
@@ -196,6 +207,7 @@ k_layered_finish(WaveParams wp, PathState st, PathState nx, SurfaceState sf, Lay
     }
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t iters = (n + stride - 1) / stride;
+    __shared__ BlockAppendScratch s_app;
     for (uint32_t it = 0; it < iters; it++) {
         const uint32_t q = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
         bool alive = false;
@@ -254,7 +266,7 @@ k_layered_finish(WaveParams wp, PathState st, PathState nx, SurfaceState sf, Lay
                 wave_out[2 * wp.capacity + id] = radiance.z;
             }
         }
-        const uint32_t jn = warp_append(alive, wc.active + bounce + 1);
+        const uint32_t jn = B2PT_APPEND(alive, wc.active + bounce + 1);
         if (alive) {
             nx.ox[jn] = next_o.x; nx.oy[jn] = next_o.y; nx.oz[jn] = next_o.z;
             nx.dx[jn] = next_d.x; nx.dy[jn] = next_d.y; nx.dz[jn] = next_d.z;

@@ -78,6 +78,33 @@ __device__ __forceinline__ uint32_t warp_append(bool want, uint32_t* counter) {
     base = __shfl_sync(0xffffffffu, base, leader);
     return base + (uint32_t)__popc(mask & ((1u << lane) - 1u));
 }
+
+// block-aggregated append: ONE atomic per block and call instead of one per warp (the queue counters are single
+// addresses every warp of the grid hits; a same-address atomic costs about half a nanosecond of L2 time and its
+// round trip sits between a warp's loads and its stores).  Every thread of the block must call this, the same number
+// of times; `trip` (the caller's loop counter) alternates the two copies of the shared scratch so that a fast warp's
+// next call cannot overwrite what a slow warp still reads.  Positions are deterministic inside the block.
+constexpr int kAppendWarps = kWaveThreads / 32;
+struct BlockAppendScratch {
+    uint32_t cnt[2][kAppendWarps];
+    uint32_t base[2];
+};
+__device__ __forceinline__ uint32_t block_append(bool want, uint32_t* counter, BlockAppendScratch& sh, uint32_t trip) {
+    const uint32_t mask = __ballot_sync(0xffffffffu, want);
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5, b = trip & 1u;
+    if (lane == 0) sh.cnt[b][warp] = (uint32_t)__popc(mask);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t tot = 0;
+#pragma unroll
+        for (int w = 0; w < kAppendWarps; w++) tot += sh.cnt[b][w];
+        sh.base[b] = tot ? atomicAdd(counter, tot) : 0u;
+    }
+    __syncthreads();
+    uint32_t pos = sh.base[b] + (uint32_t)__popc(mask & ((1u << lane) - 1u));
+    for (uint32_t w = 0; w < warp; w++) pos += sh.cnt[b][w];
+    return pos;
+}
 #endif
 
 }  // namespace b2pt

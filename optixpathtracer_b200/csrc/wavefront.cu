@@ -77,6 +77,7 @@ k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restri
     const uint32_t iters = (n + stride - 1) / stride;
     const DeviceTexFetch tex{sc.textures};
     uint32_t* qn = wc.queued + 4 * bounce;
+    __shared__ BlockAppendScratch s_app[2];
     // block-aggregated append to the light buckets; two copies, used by alternate trips of the loop
     __shared__ uint32_t s_cnt[2][kThreads / 32][kShadowBuckets];
     __shared__ uint32_t s_base[2][kShadowBuckets];
@@ -180,9 +181,15 @@ k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restri
                 sh.order[(size_t)bucket * sh.capacity + pos] = i;
             }
         }
+        if (wp.mode == B2PT_BSDF_AUTO) {   // two queues can be non-empty: conductor and layered
 #pragma unroll
-        for (int k = 0; k < 4; k++) {
-            const uint32_t pos = warp_append(kind == k, qn + k);
+            for (int k = 0; k < 4; k += 3) {
+                const uint32_t pos = block_append(kind == k, qn + k, s_app[k ? 1 : 0], it);
+                if (kind == k) queues[(size_t)k * wp.capacity + pos] = i;
+            }
+        } else {
+            const int k = wp.mode - 1;
+            const uint32_t pos = block_append(kind == k, qn + k, s_app[0], it);
             if (kind == k) queues[(size_t)k * wp.capacity + pos] = i;
         }
         n_culled += culled ? 1u : 0u;
@@ -241,6 +248,7 @@ k_shade(WaveParams wp, PathState st, PathState nx, SurfaceState sf, const uint32
     const uint32_t n = wc.queued[4 * bounce + KIND];
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t iters = (n + stride - 1) / stride;
+    __shared__ BlockAppendScratch s_app;
     for (uint32_t it = 0; it < iters; it++) {
         const uint32_t q = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
         bool alive = false;
@@ -277,7 +285,7 @@ k_shade(WaveParams wp, PathState st, PathState nx, SurfaceState sf, const uint32
                 wave_out[2 * wp.capacity + id] = pv.radiance.z;
             }
         }
-        const uint32_t j = warp_append(alive, wc.active + bounce + 1);
+        const uint32_t j = block_append(alive, wc.active + bounce + 1, s_app, it);
         if (alive) {
             nx.ox[j] = pv.next_o.x; nx.oy[j] = pv.next_o.y; nx.oz[j] = pv.next_o.z;
             nx.dx[j] = pv.next_d.x; nx.dy[j] = pv.next_d.y; nx.dz[j] = pv.next_d.z;
