@@ -450,6 +450,17 @@ def run_b2pt(args, cfg):
                                 "thread_instructions_per_task": prof.get("k_layered_engine_thread_inst_per_task"),
                                 "source": prof.get("k_layered_engine_source", "profiles/ (ncu --set full)")},
                     "traversal": k5}
+        # the bound that does apply: thread instructions per second against what the SMs can issue
+        # (SMs x 4 schedulers x 32 lanes x SM clock) = issue-slot utilisation x lanes per instruction
+        tipt = prof.get("k_layered_engine_thread_inst_per_task")
+        sm_mhz = (clocks or {}).get("sm_mhz") or 1965.0
+        if tipt:
+            import torch as _t
+            sms = _t.cuda.get_device_properties(local).multi_processor_count
+            peak_ti = sms * 4 * 32 * sm_mhz * 1e6
+            roofline["limiter"]["thread_instructions_per_s"] = roofline["walk_tasks_per_s"] * tipt
+            roofline["limiter"]["issue_peak_thread_instructions_per_s"] = peak_ti
+            roofline["limiter"]["issue_roofline_frac"] = roofline["walk_tasks_per_s"] * tipt / peak_ti
     else:
         roofline = dict(k5)
         roofline.update({"bound": "hbm", "peak": peak, "peak_source": peak_src,

@@ -32,10 +32,10 @@ namespace {
 #endif
 
 constexpr uint32_t kNoF = 0xffffffffu;
-// K7d-p / K7d-f are gather / scatter kernels bound by memory latency (ncu: 12-16 % of the issue slots used), but more
-// resident threads do not help them: built for 16 blocks per SM (32 registers, 28-40 bytes of spills) they were 10-30 %
-// SLOWER (prep 0.78 -> 1.02 ms, finish 1.50 -> 1.66 ms per c4 launch, c4 573 -> 549 Msamples/s,
-// profiles/r02_ab_prep_finish_occupancy.txt): the grid stays at 8 blocks per SM with the registers the compiler wants
+// K7d-p / K7d-f are gather / scatter kernels.  What held them at 3 TB/s was the queue atomic (one same-address atomic per warp
+// and trip; B2PT_APPEND below: one per block, finish 77 % of the DRAM peak, profiles/r02_ab_atomics.txt) — not occupancy:
+// built for 16 blocks per SM (32 registers, 28-40 bytes of spills) they were 10-30 % SLOWER
+// (profiles/r02_ab_prep_finish_occupancy.txt), so the grid stays at 8 blocks per SM with the registers the compiler wants
 constexpr int kPrepGrid = 8;
 
 // scratch of one bounce, `capacity` slots per plane (B2ptRenderer::d_layered)
