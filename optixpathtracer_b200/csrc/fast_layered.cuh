@@ -91,8 +91,12 @@ struct WalkKey {
     uint32_t c2;       // walk id: 0..4 f walks, 5 the sample walk
 };
 constexpr uint32_t kStageWalk = 2;   // stage 0 = K6 surface, 1 = serial shade kernels
+// RNG = 0: the out-of-line ten-round block every other draw site calls; 10 / 7: the block inlined here with that many
+// rounds (the engine's A/B, B2PT_WALK_RNG: the Philox rounds are 15 % of the engine's instructions)
+template <int RNG>
 B2PT_HD Draws walk_draws(const WalkKey& k, int step) {
-    return draws_from_block(philox_block((uint32_t)step, k.c1, k.c2, k.k0, k.k1));
+    if constexpr (RNG == 0) return draws_from_block(philox_block((uint32_t)step, k.c1, k.c2, k.k0, k.k1));
+    else return draws_from_block(philox_block_inline<RNG>((uint32_t)step, k.c1, k.c2, k.k0, k.k1));
 }
 // Russian-roulette uniforms are needed rarely (depth > 3 and throughput < 1/4): drawn on demand from a side block
 B2PT_HD float walk_rr_uniform(const WalkKey& k, int step, int which) {
@@ -356,9 +360,10 @@ B2PT_HD bool walk_roulette(Walk& k, const WalkKey& key, int depth, int which) {
 // its lanes meet again to the end of the function, so that the two heavy blocks (the visible-normal sample of
 // the top event, the next-event term of the bottom event) would run once per GROUP of lanes instead of once per
 // warp (measured: 11.9 active lanes per instruction instead of 20, profiles/r02_k_layered_engine_*).
+template <int RNG = 0>
 B2PT_HD bool walk_step(Walk& k, const WalkKey& key) {
     const int st = k.step;
-    const Draws u = walk_draws(key, st);
+    const Draws u = walk_draws<RNG>(key, st);
     const bool smooth = k.alpha < 1e-3f;
     const float a2 = k.alpha * k.alpha;
     const bool is_f = k.is_f;

@@ -80,11 +80,13 @@ struct LcgRng {
     }
 };
 
-// Philox4x32-10 (Salmon et al., SC'11).
-B2PT_HD void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
-                           uint32_t k0, uint32_t k1, uint32_t out[4]) {
+// Philox4x32-R (Salmon et al., SC'11); R = 10 is the generator's standard strength (7 is the paper's smallest
+// Crush-resistant round count: the walk engine's A/B, fast_layered.cuh)
+template <int ROUNDS>
+B2PT_HD void philox4x32(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                        uint32_t k0, uint32_t k1, uint32_t out[4]) {
 #pragma unroll
-    for (int r = 0; r < 10; r++) {
+    for (int r = 0; r < ROUNDS; r++) {
         const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
         const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
         const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
@@ -97,10 +99,22 @@ B2PT_HD void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
+B2PT_HD void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                           uint32_t k0, uint32_t k1, uint32_t out[4]) {
+    philox4x32<10>(c0, c1, c2, c3, k0, k1, out);
+}
+
 // one 4-draw block; a real call on the device (ten rounds x every draw site is a lot of code)
 B2PT_HD_CALL uint4 philox_block(uint32_t block, uint32_t c1, uint32_t c2, uint32_t k0, uint32_t k1) {
     uint32_t o[4];
     philox4x32_10(block, c1, c2, 0x62327074u /* "b2pt" */, k0, k1, o);
+    return make_uint4(o[0], o[1], o[2], o[3]);
+}
+// the same block inlined at its one call site per walk step (the walk engine: one draw site, a small loop)
+template <int ROUNDS>
+B2PT_HD uint4 philox_block_inline(uint32_t block, uint32_t c1, uint32_t c2, uint32_t k0, uint32_t k1) {
+    uint32_t o[4];
+    philox4x32<ROUNDS>(block, c1, c2, 0x62327074u /* "b2pt" */, k0, k1, o);
     return make_uint4(o[0], o[1], o[2], o[3]);
 }
 

@@ -120,7 +120,7 @@ k_layered_prep(WaveParams wp, PathState st, SurfaceState sf, LayeredScratch ls, 
 // ---- K7d-e -------------------------------------------------------------------------------------
 // REFILL = idle lanes that trigger a task fetch.  A fetched lane starts at step 0 while its neighbours are
 // mid-walk; that costs nothing extra because every step has the same shape (fast_layered.cuh).
-template <int REFILL, int MINB>
+template <int REFILL, int MINB, int RNG = 10>
 __global__ void __launch_bounds__(kWaveThreads, MINB)
 k_layered_engine(LayeredScratch ls, const uint32_t* __restrict__ lq, const uint32_t* __restrict__ queued,
                  uint32_t* __restrict__ lcounts, uint32_t bounce) {
@@ -180,7 +180,7 @@ k_layered_engine(LayeredScratch ls, const uint32_t* __restrict__ lq, const uint3
             if (exhausted) break;
             continue;
         }
-        if (k.step >= 0 && !walk_step(k, key)) {
+        if (k.step >= 0 && !walk_step<RNG>(k, key)) {
             if (k.is_f) {
                 float* fp = ls.fpart + (size_t)key.c2 * 3u * ls.capacity + out;
                 fp[0] = k.f.x;
@@ -332,6 +332,16 @@ void launch_layered_walks(B2ptRenderer* r, const WaveParams& wp, const WaveCount
     // whole idle half-warp does not cost more than that), B2PT_ENGINE_OCC = blocks per SM (4 | 6 | 8)
     static const int refill = [] { const char* e = getenv("B2PT_ENGINE_REFILL"); return e ? atoi(e) : 16; }();
     static const int occ = [] { const char* e = getenv("B2PT_ENGINE_OCC"); return e ? atoi(e) : 6; }();
+    // The Philox block of a walk step is inlined in the engine (RNG = 10: engine 94.7 -> 91.8 ms per c4 step against the
+    // out-of-line call the other draw sites use).  B2PT_WALK_RNG=7 (A/B, default refill / occupancy only): seven rounds
+    // instead of ten, the smallest Crush-resistant count of the Philox paper: 88.6 ms, c4 603 -> 613 Msamples/s
+    // (profiles/r02_ab_walk_rng.txt); B2PT_WALK_RNG=0: the out-of-line call.  Ten rounds stay the default.
+    static const int walk_rng = [] { const char* e = getenv("B2PT_WALK_RNG"); return e ? atoi(e) : 10; }();
+    if (walk_rng == 0 || walk_rng == 7) {
+        if (walk_rng == 0) k_layered_engine<16, 6, 0><<<r->sm_count * 6, kWaveThreads, 0, s>>>(ls, lq, wc.queued, lcounts, bounce);
+        else k_layered_engine<16, 6, 7><<<r->sm_count * 6, kWaveThreads, 0, s>>>(ls, lq, wc.queued, lcounts, bounce);
+        return;
+    }
 #define B2PT_ENGINE(R, O) k_layered_engine<R, O><<<r->sm_count * O, kWaveThreads, 0, s>>>(ls, lq, wc.queued, lcounts, bounce)
     if (occ >= 8) {
         if (refill >= 32) B2PT_ENGINE(32, 8); else if (refill >= 16) B2PT_ENGINE(16, 8); else if (refill >= 8) B2PT_ENGINE(8, 8);

@@ -283,7 +283,9 @@ WarpPolicy warp_policy() {
         const char* b = getenv("B2PT_BREAK");
         const char* sc = getenv("B2PT_SMALL_CHUNKS");
         const char* au = getenv("B2PT_ANY_UNSORTED");
-        return WarpPolicy{a ? atoi(a) : 8, b ? atoi(b) : 16, sc ? atoi(sc) : 1, au ? atoi(au) : 1};
+        const char* ba = getenv("B2PT_BREAK_ANY");
+        // break thresholds 16 (K5) / 20 (K8): profiles/r02_ab_warp_policy.txt
+        return WarpPolicy{a ? atoi(a) : 8, b ? atoi(b) : 16, sc ? atoi(sc) : 1, au ? atoi(au) : 1, ba ? atoi(ba) : (b ? atoi(b) : 20)};
     }();
     return v;
 }

@@ -82,6 +82,7 @@ struct WarpPolicy {
     int break_lanes;    // leave the descent when this many lanes cannot descend (hold two leaves / are done)
     int small_chunks;   // 1: launches with fewer than 64 rays per warp use smaller chunks (ray_chunk_shift)
     int any_unsorted;   // 1: occlusion rays visit the hit children of a wide node in slot order, not nearest first
+    int break_lanes_any;   // break_lanes of the wide occlusion kernel (its leaves end rays: it pays to wait for more of them)
 };
 
 // ... unless the launch is small.  The late bounces of a wave hold a few thousand rays (c2: 0.06 % of the paths

@@ -196,7 +196,7 @@ __device__ __forceinline__ void trace_wide(const void* __restrict__ nodes_v, con
                 }
               }
               const bool stopped = node < 0 || node == kStackSentinel;
-              if ((int)__popc(__ballot_sync(kFullMask, stopped)) >= pol.break_lanes) break;
+              if ((int)__popc(__ballot_sync(kFullMask, stopped)) >= (ANY ? pol.break_lanes_any : pol.break_lanes)) break;
             }
             const uint32_t tris_before = ts.tris;
             while (pend < 0) {

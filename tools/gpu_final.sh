@@ -1,5 +1,5 @@
 #!/bin/bash
-# round 2, GPU call 16: the round's final build - whole GPU tier, the driver's bench line (c4) + reference arm, every other config,
+# round 2, final-build measurement (calls 16 and 20): the round's final build - whole GPU tier, the driver's bench line (c4) + reference arm, every other config,
 # task census of the engine launch the ncu capture shows (bounce 0, 16 spp)
 cd "$GRAFT_REPO_ROOT" 2>/dev/null || true
 export B2PT_NO_REBUILD=1
@@ -33,3 +33,15 @@ with OptixRenderer(None, sc, bsdf_mode=mode, rng_mode="philox", max_bounces=1) a
     st = r.Stats()
     print("ENGINE_TASKS bounce0 16spp", {k: st[k] for k in ("walk_f_hits", "walk_s_hits", "radiance_rays", "shadow_rays", "shadow_rays_traced")})
 PY
+# evidence captures (each after its own command exited 0 without ncu): launch list, one full capture per kernel (bounce 0 of a
+# 16-spp wave), the bounce-2 launches of the traversal kernels (incoherent rays); summaries: tools/ncu_summary.py, tools/launch_summary.py
+if [ "${B2PT_CAPTURE:-0}" = 1 ]; then
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 300 --csv --log-file gpurun_out/final_launches_c4.csv python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/final_ncu_launches.log 2>&1; echo "ncu launches exit $?"
+  for k in k_layered_engine k_closest_w k_any_w k_surface k_layered_prep k_layered_finish k_raygen k_accumulate; do
+    timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k -c 1 -o gpurun_out/final_$k python bench.py --steps 1 --warmup 0 --spp-per-step 16 --no-cpu-baseline > gpurun_out/final_ncu_$k.log 2>&1; echo "ncu $k exit $?"
+  done
+  for k in k_closest_w k_any_w; do
+    timeout 600 ncu --set full --clock-control none --import-source on -k regex:$k -s 2 -c 1 -o gpurun_out/final_${k}_b2 python bench.py --steps 1 --warmup 0 --spp-per-step 16 --no-cpu-baseline > gpurun_out/final_ncu_${k}_b2.log 2>&1; echo "ncu $k b2 exit $?"
+  done
+  timeout 1500 python tools/image_parity.py --size 256 --spp 64 --out gpurun_out/final_image_parity.json > gpurun_out/final_image_parity.log 2>&1; echo "image parity exit $?"
+fi
