@@ -207,17 +207,20 @@ B2PT_HD void tri_unpack(const TriRecord& r, float3& v0, float3& v1, float3& v2) 
     v1 = v3(r.a.w, r.b.x, r.b.y);
     v2 = v3(r.b.z, r.b.w, r.c.x);
 }
-B2PT_HD TriRecord tri_pack(float3 v0, float3 v1, float3 v2, uint32_t prim, uint32_t mesh) {
+// flags (c.w, as bits): 1 = the triangle's mesh has an alpha cut-out texture — the any-hit predicate must see its hits
+// (the wide kernels read the flag with the record instead of chasing materials[mesh] for every triangle they test)
+B2PT_HD TriRecord tri_pack(float3 v0, float3 v1, float3 v2, uint32_t prim, uint32_t mesh, uint32_t flags = 0u) {
     TriRecord r;
     r.a = make_float4(v0.x, v0.y, v0.z, v1.x);
     r.b = make_float4(v1.y, v1.z, v2.x, v2.y);
 #if defined(__CUDA_ARCH__)
-    r.c = make_float4(v2.z, __uint_as_float(prim), __uint_as_float(mesh), 0.0f);
+    r.c = make_float4(v2.z, __uint_as_float(prim), __uint_as_float(mesh), __uint_as_float(flags));
 #else
-    float fp, fm;
+    float fp, fm, ff;
     __builtin_memcpy(&fp, &prim, 4);
     __builtin_memcpy(&fm, &mesh, 4);
-    r.c = make_float4(v2.z, fp, fm, 0.0f);
+    __builtin_memcpy(&ff, &flags, 4);
+    r.c = make_float4(v2.z, fp, fm, ff);
 #endif
     return r;
 }

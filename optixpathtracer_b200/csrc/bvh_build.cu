@@ -557,8 +557,8 @@ k_emit_tris(int n, const float3* __restrict__ wv, const float* __restrict__ norm
     if (s >= n) return;
     const uint32_t g = order[s];
     const uint32_t m = tri_mesh[g];
-    tris[s] = tri_pack(wv[3 * g], wv[3 * g + 1], wv[3 * g + 2], g, m);
     const MeshInfo& mi = meshes[m];
+    tris[s] = tri_pack(wv[3 * g], wv[3 * g + 1], wv[3 * g + 2], g, m, mi.cutout ? 1u : 0u);
     const int i0 = indices[3 * g] + mi.vtx_offset, i1 = indices[3 * g + 1] + mi.vtx_offset,
               i2 = indices[3 * g + 2] + mi.vtx_offset;
     float3 n0 = v3(0.0f), n1 = v3(0.0f), n2 = v3(0.0f);
@@ -677,6 +677,15 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
     std::vector<uint32_t> tri_mesh((size_t)n_tri);
     std::vector<MeshInfo> infos((size_t)desc.n_meshes);
     std::vector<MaterialRecord> mats((size_t)desc.n_meshes);
+    std::vector<char> texture_opaque((size_t)std::max(desc.n_textures, 0), 0);
+    for (int t = 0; t < desc.n_textures; t++) {
+        const B2ptTexture& tx = desc.textures[t];
+        if (!tx.rgba || tx.width <= 0 || tx.height <= 0) continue;
+        bool opaque = true;
+        const size_t n_px = (size_t)tx.width * (size_t)tx.height;
+        for (size_t i = 0; i < n_px && opaque; i++) opaque = tx.rgba[4 * i + 3] == 255;
+        texture_opaque[(size_t)t] = opaque ? 1 : 0;
+    }
     int64_t vo = 0, to = 0;
     int any_alpha = 0;
     for (int m = 0; m < desc.n_meshes; m++) {
@@ -687,6 +696,7 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
         mi.tri_offset = (int32_t)to;
         mi.has_normals = me.normals != nullptr;
         mi.has_uv = me.texcoords != nullptr;
+        mi.cutout = 0;
         if (me.n_vertices) {
             memcpy(&pos[vo * 3], me.positions, (size_t)me.n_vertices * 12);
             if (me.normals) memcpy(&nrm[vo * 3], me.normals, (size_t)me.n_vertices * 12);
@@ -709,7 +719,14 @@ void build_scene(const B2ptSceneDesc& desc, SceneBuffers& out, cudaStream_t stre
         mr.tex_normal = tex_ok(me.tex_normal);
         mr.tex_metal_rough = tex_ok(me.tex_metal_rough);
         memcpy(mr.mcol, me.model, sizeof mr.mcol);
-        if (mr.tex_albedo >= 0) any_alpha = 1;  // meshes without texcoords read uv = (0,0)
+        // The any-hit predicate (alpha.cuh) can only reject where the albedo texture's alpha is below 0.9 after the sRGB
+        // decode.  A texture whose texels all carry alpha 255 filters to exactly 1.0 (oracle/texunit.h: 8-bit weights that
+        // sum to 256 over 16-bit unorm texels) and accepts every hit: its meshes — the usual case of an opaque albedo
+        // map — trace like untextured ones.  Meshes without texcoords read uv = (0,0).
+        if (mr.tex_albedo >= 0 && !texture_opaque[(size_t)mr.tex_albedo]) {
+            mi.cutout = 1;
+            any_alpha = 1;
+        }
         vo += me.n_vertices;
         to += me.n_triangles;
     }

@@ -38,6 +38,7 @@ struct MeshInfo {
     int32_t tri_offset;
     int32_t has_normals;
     int32_t has_uv;
+    int32_t cutout;   // the mesh has an albedo texture whose alpha can reject a hit (some texel below 255): TriRecord::c.w
 };
 
 // POD view handed to kernels by value.

@@ -102,6 +102,32 @@ __device__ __noinline__ Candidate resolve_in_fp64(const TriRecord* __restrict__ 
     return c;
 }
 
+// The same decision for a triangle `x` whose fp64 evaluation the caller already holds (it accepted the hit at distance tx,
+// inside the ray's range: the alpha cut-out path of the wide kernels): only the current candidate may still need its own.
+__device__ __noinline__ Candidate resolve_known(const TriRecord* __restrict__ tris, float3 o, float3 d, int x, double tx,
+                                                uint32_t prim_x, Candidate c) {
+    const float x_lo = __double2float_rd(tx), x_hi = __double2float_ru(tx);
+    bool x_wins = c.slot < 0 || x_hi < c.lo;
+    if (!x_wins && !(x_lo > c.hi)) {   // unordered: the candidate's fp64 value decides, ties to the lower primitive id
+        const TriRecord* cp = tris + c.slot;
+        const float4 ca = B2PT_LDG4(&cp->a), cb = B2PT_LDG4(&cp->b), cc = B2PT_LDG4(&cp->c);
+        double tc, uc, vc;
+        bool bfc;
+        const bool ok = tri_exact(o, d, v3(ca.x, ca.y, ca.z), v3(ca.w, cb.x, cb.y), v3(cb.z, cb.w, cc.x), tc, uc, vc, bfc);
+        x_wins = !ok || tx < tc || (tx == tc && prim_x < f2u_bits(cc.y));
+        if (!x_wins) {
+            c.lo = __double2float_rd(tc);
+            c.hi = __double2float_ru(tc);
+        }
+    }
+    if (x_wins) {
+        c.slot = x;
+        c.lo = x_lo;
+        c.hi = x_hi;
+    }
+    return c;
+}
+
 // Io: bool load(uint32_t i, float3& o, float3& d, float& tmax);  void store_slot(uint32_t i, int slot /* -1: miss */)
 template <bool STATS, class Io>
 __device__ __forceinline__ void trace_closest_deferred(const BvhNode2* __restrict__ nodes,

@@ -272,6 +272,11 @@ int shared_stack_levels() {
     }();
     return v;
 }
+// blocks per SM of the alpha-predicate instantiation (B2PT_ALPHA_OCC = 6 | 7; A/B: profiles/r02_ab_cutout.txt)
+int alpha_occ() {
+    static const int v = [] { const char* e = getenv("B2PT_ALPHA_OCC"); return e ? atoi(e) : 7; }();
+    return v;
+}
 constexpr int kWideOcc = 7;   // resident blocks per SM the wide kernels are built for (A/B: profiles/r01_ab_traversal_occupancy.txt)
 int occ_blocks() {            // ... and the binary ones: B2PT_OCC = 4 | 6 | 8 (default) | 10
     static const int v = [] { const char* e = getenv("B2PT_OCC"); return e ? atoi(e) : 8; }();
@@ -318,7 +323,9 @@ int trace_node_bytes(const DeviceScene&) {
             if (alpha) { if (s6) KERNEL<true, 4, 6, true> ARGS; else KERNEL<true, 4, 5, true> ARGS; }        \
             else       { if (s6) KERNEL<true, 4, 6, false> ARGS; else KERNEL<true, 4, 5, false> ARGS; }      \
         } else if (alpha) {                                                                    \
-            if (s6) KERNEL<false, 6, 6, true> ARGS; else KERNEL<false, 6, 5, true> ARGS;       \
+            if (!s6) KERNEL<false, 6, 5, true> ARGS;                                           \
+            else if (alpha_occ() == 6) KERNEL<false, 6, 6, true> ARGS;                         \
+            else KERNEL<false, kWideOcc, 6, true> ARGS;                                        \
         } else if (!s6) {                                                                      \
             KERNEL<false, kWideOcc, 5, false> ARGS;                                            \
         } else if (ss == 24) {                                                                 \

@@ -35,6 +35,23 @@ namespace b2pt {
         tk[k] = tn <= fmaf(tf, 1.000001f, eslack) ? tn : INFINITY;                                            \
     }
 
+// A triangle of a cut-out mesh that passed the fp32 filter: exact evaluation, predicate at its (u, v), and — closest-hit
+// rays — the candidate update with the fp64 distance in hand.  One copy, out of line.
+template <class Accept>
+__device__ __noinline__ Candidate cutout_triangle(const TriRecord* __restrict__ tris, const Accept& accept, float3 o, float3 d,
+                                                  float tmin, float tmax, int slot, uint32_t mesh, uint32_t prim, Candidate c,
+                                                  bool any, bool& accepted) {
+    const TriRecord* tp = tris + slot;
+    const float4 ta = B2PT_LDG4(&tp->a), tb = B2PT_LDG4(&tp->b);
+    const float tcx = __ldg(&tp->c.x);
+    double t, u, v;
+    bool bf;
+    accepted = tri_exact(o, d, v3(ta.x, ta.y, ta.z), v3(ta.w, tb.x, tb.y), v3(tb.z, tb.w, tcx), t, u, v, bf) &&
+               t > (double)tmin && t < (double)tmax && accept((uint32_t)slot, mesh, (float)u, (float)v);
+    if (accepted && !any) c = resolve_known(tris, o, d, slot, t, prim, c);
+    return c;
+}
+
 // ANY = false: closest hit, deferred (Io::store_slot).  ANY = true: occlusion (Io::store(i, hit, occluded)).
 // The node step: FMA-form slabs (above), branch-free pushes while the stack stays inside its shared-memory
 // levels, an unconditional read of the stack top instead of a divergent pop.
@@ -212,32 +229,33 @@ __device__ __forceinline__ void trace_wide(const void* __restrict__ nodes_v, con
                 const float4 ta = B2PT_LDG4(&tp->a);
                 const float4 tb = B2PT_LDG4(&tp->b);
                 float tcx;
-                uint32_t mesh = 0;
+                uint32_t mesh = 0, prim = 0;
+                bool textured = false;
                 if constexpr (kPredicate) {
+                    // the cut-out flag rides in the record (TriRecord::c.w, bvh.cuh): no materials[mesh] load per test
                     const float4 tc = B2PT_LDG4(&tp->c);
                     tcx = tc.x;
+                    prim = f2u_bits(tc.y);
                     mesh = f2u_bits(tc.z);
+                    textured = f2u_bits(tc.w) != 0u;
                 } else {
                     tcx = __ldg(&tp->c.x);
                 }
                 const float3 v0 = v3(ta.x, ta.y, ta.z), v1 = v3(ta.w, tb.x, tb.y), v2 = v3(tb.z, tb.w, tcx);
-                bool textured = false;
-                if constexpr (kPredicate) textured = accept.textured(mesh);
                 if (textured) {
-                    // the predicate needs the exact u, v: filter -> fp64 -> texel, as the binary kernels do
+                    // the predicate needs the exact u, v: filter -> fp64 -> texel, as the binary kernels do — out of line
+                    // (cutout_triangle), so that the registers of the fp64 test and of the texture fetch are not held
+                    // through the node loop: untextured geometry of a textured scene runs the untextured kernel's code
                     if (tri_filter(r.o, r.d, r.d_l1, v0, v1, v2, tmin, ANY ? tmax_f : c.hi)) {
                         if (STATS) ts.exact++;
-                        double t, u, v;
-                        bool bf;
-                        if (tri_exact(r.o, r.d, v0, v1, v2, t, u, v, bf) && t > (double)tmin && t < (double)tmax_f &&
-                            accept((uint32_t)slot, mesh, (float)u, (float)v)) {
-                            if constexpr (ANY) {
+                        bool accepted = false;
+                        c = cutout_triangle(tris, accept, r.o, r.d, tmin, tmax_f, slot, mesh, prim, c, ANY, accepted);
+                        if constexpr (ANY) {
+                            if (accepted) {
                                 occluded = true;
                                 node = kStackSentinel;
                                 pend = 0;
                                 break;
-                            } else {
-                                c = resolve_in_fp64(tris, r.o, r.d, tmin, tmax_f, slot, c);
                             }
                         }
                     }

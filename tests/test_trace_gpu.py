@@ -163,6 +163,33 @@ def test_multi_triangle_leaves(oracle, leaf):
         assert n_wide <= r1.Stats()["n_wide_nodes"] and (leaf == 1 or n_wide < r1.Stats()["n_wide_nodes"])
 
 
+def test_opaque_albedo_texture_traces_like_an_untextured_mesh(oracle):
+    """The any-hit predicate (devicePrograms.cu:518-561) can only reject where the albedo texture's alpha is below 0.9:
+    a texture whose texels all carry alpha 255 accepts every hit, so its meshes take the traversal path of untextured
+    ones (TriRecord flag, bvh_build.cu) — same hits as the brute force WITHOUT a predicate, bit for bit.  One texel
+    below 255 and the mesh is a cut-out mesh again: rays through that texel's area change their hit."""
+    sc = cases.small_spheres()
+    soup, _ = scenes.scene_triangle_soup(sc)
+    o, d = cases.scene_rays(sc, 64, 48, 3000, seed=9)
+    tex = np.full((8, 8, 4), 255, np.uint8)
+    tex[..., :3] = 120
+    for me in sc["meshes"]:
+        me["tex_albedo"] = 0
+        if me.get("texcoords") is None:
+            me["texcoords"] = np.zeros((len(me["positions"]), 2), f32)
+    sc["textures"] = [tex]
+    with _renderer(sc) as r:
+        prim_opaque, *_ = _compare(r, oracle, soup, o, d)
+        tm = np.full(len(o), 6.0, f32)
+        assert np.array_equal(r.TraceAny(o, d, tm), oracle.any(soup, o, d, tm))
+    holes = tex.copy()
+    holes[..., 3] = 0                          # fully transparent: every hit of a textured mesh is ignored
+    sc["textures"] = [holes]
+    with _renderer(sc) as r:
+        gp, *_ = r.TraceClosest(o, d, 0.0, 100.0)
+        assert (gp == -1).all() and (prim_opaque >= 0).any()
+
+
 def test_far_origins_small_triangles(oracle):
     rng = np.random.default_rng(11)
     c = rng.uniform(-1, 1, (4000, 1, 3))
@@ -315,7 +342,9 @@ def _deep_textured_scene():
     sc = _soup_scene(soup)
     sc["meshes"][0]["texcoords"] = np.zeros((len(soup) * 3, 2), f32)
     sc["meshes"][0]["tex_albedo"] = 0
-    sc["textures"] = [np.full((2, 2, 4), 255, np.uint8)]
+    tex = np.full((2, 2, 4), 255, np.uint8)
+    tex[1, 1, 3] = 0          # one transparent texel: a cut-out texture (an opaque one would trace like no texture at all)
+    sc["textures"] = [tex]
     return sc
 
 
