@@ -410,13 +410,14 @@ def run_b2pt(args, cfg):
     engine_ms, engine_n = st_attr["device_ms_engine"], st_attr["launches_engine"]
     shares = {"closest": ms_k[0] / attr_ms, "any": ms_k[1] / attr_ms, "surface": ms_k[2] / attr_ms,
               "shade": ms_k[3] / attr_ms, "other": ms_k[4] / attr_ms, "walk_engine": engine_ms / attr_ms}
-    prof = {}
+    prof, all_prof = {}, {}
     ppath = ROOT / "profiles" / "traffic.json"
     if ppath.exists():
         try:
-            prof = json.load(open(ppath)).get(args.config, {})
+            all_prof = json.load(open(ppath))
+            prof = all_prof.get(args.config, {})
         except Exception:
-            prof = {}
+            prof, all_prof = {}, {}
     closest_ms = max(ms_k[0], 1e-9)
     k5 = {"kernel": "k_closest_w (K5 closest-hit BVH traversal)",
           "achieved": st_attr["radiance_rays"] * bpr["closest"] / (closest_ms * 1e-3) / 1e9, "unit": "GB/s",
@@ -427,8 +428,9 @@ def run_b2pt(args, cfg):
           "dram_bytes_per_ray": prof.get("k_closest_dram_bytes_per_ray"),
           "shadow": {"achieved": st_attr["shadow_rays_traced"] * bpr["any"] / (max(ms_k[1], 1e-9) * 1e-3) / 1e9,
                      "bytes_per_ray": bpr["any"]},
-          "limiter": "l1tex wavefronts + dependent-fetch latency: the algorithmic bytes are served by L1/L2 (DRAM sees "
-                     "dram_bytes_per_ray, ncu), so `achieved` against the HBM peak measures work, not a bandwidth bound"}
+          "limiter": "l1tex wavefronts + instruction issue: the algorithmic bytes are served by L1/L2 (DRAM sees "
+                     "dram_bytes_per_ray, ncu), so `achieved` against the HBM peak measures work, not a bandwidth bound",
+          "limits_ncu": all_prof.get("k_closest_limits_readme_scene")}
     k5["frac"] = k5["achieved"] / peak
     if engine_ms > max(ms_k[0], ms_k[1]):
         # the layered walk engine dominates (c4): its algorithmic bytes are the task records it reads and the
