@@ -82,14 +82,20 @@ k_surface(WaveParams wp, DeviceScene sc, PathState st, const HitRecord* __restri
     __shared__ uint32_t s_cnt[2][kThreads / 32][kShadowBuckets];
     __shared__ uint32_t s_base[2][kShadowBuckets];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    // the hit of the NEXT trip is fetched a trip ahead: the kernel is a chain of dependent loads (hit -> triangle -> normals,
+    // uvs, material -> texels) at half occupancy, and this takes the first link off it
+    const uint32_t i0 = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t tri_next = i0 < n ? hits[i0].tri : kHitMiss;
     for (uint32_t it = 0; it < iters; it++) {
-        const uint32_t i = it * stride + blockIdx.x * blockDim.x + threadIdx.x;
+        const uint32_t i = it * stride + i0;
         int kind = -1;
         int bucket = -1;   // light bucket of this slot's shadow ray, -1: none
         bool culled = false;
+        const uint32_t tri_now = tri_next;
+        if (i + stride < n) tri_next = hits[i + stride].tri;
         if (i < n) {
             HitRecord hit;
-            hit.tri = hits[i].tri;
+            hit.tri = tri_now;
             hit.t = hit.u = hit.v = 0.0f;
             // K5 decided WHICH triangle is hit (trace_deferred.cuh); its t, u, v and back-face flag — the
             // fp64 evaluation of that one triangle — are computed here, where every lane has a hit
